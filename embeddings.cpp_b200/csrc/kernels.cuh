@@ -1,0 +1,107 @@
+// Device-side interface of the encoder forward: plain structs + launcher prototypes.
+// Every launcher enqueues on the given stream and returns the CUDA error of the launch.
+#pragma once
+#include <cuda.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200 {
+
+// weight types = the model file's ftype field (reference bert.cpp:499-521)
+enum WType : int { W_F32 = 0, W_F16 = 1, W_Q4_0 = 2, W_Q4_1 = 3 };
+
+// epilogue flags of the GEMM
+enum : int { EPI_BIAS = 1, EPI_GELU = 2, EPI_RESIDUAL = 4, EPI_FAKEQUANT = 8 };
+
+// A dense weight matrix W[N][K] (K contiguous = the file's ne0, reference bert.cpp:611-623)
+// resident in HBM in its GEMM-ready form:
+//   f32 / f16 files : `w16` fp16 [N][K] row-major (+ TMA map, box 64 x BN)
+//   q4_0 / q4_1     : 4-bit planes tiled by 64-wide k-stage so that one stage of any row
+//                     range is contiguous:
+//                       qnib  [K/64][N][2] x 16 B   (nibble order: see repack_q4 in upload.cu)
+//                       qd    [K/64][N][2] fp16     block scales d
+//                       qm    [K/64][N][2] fp16     block mins m (q4_1 only)
+//                     HBM holds 4.5 (q4_0) / 5 (q4_1) bits per weight, as in the file.
+struct DevWeight {
+    int type = W_F16;          // W_F16 (covers f32 files cast to f16) / W_Q4_0 / W_Q4_1
+    int N = 0, K = 0;
+    const __half * w16 = nullptr;
+    const uint4 * qnib = nullptr;
+    const __half * qd = nullptr;
+    const __half * qm = nullptr;
+    const float * bias = nullptr;   // [N] f32
+    int bn = 0;                     // N-tile the TMA map was encoded for
+    CUtensorMap tmap;               // B operand map (f16 mode)
+};
+
+struct GemmArgs {
+    const CUtensorMap * tmap_a;     // host pointer to the A map (copied into kernel params)
+    const __half * a;               // A [M][K] fp16 (used by the SIMT validation kernel only)
+    const DevWeight * w;
+    const __half * residual;        // [M][N] fp16 or null
+    __half * out;                   // [M][N] fp16
+    int M;                          // valid rows
+    int epilogue;                   // EPI_* flags
+    int fq_type;                    // W_Q4_0 -> q8_0 rule, W_Q4_1 -> q8_1 rule (EPI_FAKEQUANT)
+};
+
+int gemm_pick_bn(int N);              // N-tile (256/192/128/64) used for a weight with N rows
+cudaError_t launch_gemm_tc(const GemmArgs & g, int num_sms, cudaStream_t st);
+cudaError_t launch_gemm_simt(const GemmArgs & g, cudaStream_t st);      // validation kernel
+
+// Embedding table as stored for the gather kernel (K0).
+struct DevTable {
+    int type = W_F32;               // file type of the word table
+    int rows = 0, H = 0;
+    const void * data = nullptr;    // f32 [rows][H] | f16 [rows][H] | q4 nibbles [rows][H/32] x 16 B (file order)
+    const __half * qd = nullptr;    // [rows][H/32]
+    const __half * qm = nullptr;
+};
+
+// K0: x[t] = LN(word[ids[t]] + postype[pos(t)]) * g + b  -> fp16 (and its q8 fake-quant twin)
+cudaError_t launch_embed_ln(const DevTable & word, const float * postype /*[n_max][H] f32*/,
+                            const float * gamma, const float * beta,
+                            const int32_t * ids, const int32_t * cu_seqlens, int n_sent, int T, int H,
+                            __half * out, __half * out_fq, int fq_type, cudaStream_t st);
+
+// K3: y = LN(x) * g + b, x already holds GEMM + bias + residual (fp16)
+cudaError_t launch_ln(const __half * x, const float * gamma, const float * beta, int T, int H,
+                      __half * out, __half * out_fq, int fq_type, cudaStream_t st);
+
+// K2: per (sentence, head) softmax(Q K^T / sqrt(d)) V over the sentence's own tokens.
+// qkv [T][3H] fp16 (Q | K | V, head h at columns h*d), out [T][H] fp16.
+cudaError_t launch_attention(const __half * qkv, const int32_t * cu_seqlens, int n_sent, int max_len,
+                             int n_head, int d_head, __half * out, int fq_type, cudaStream_t st);
+cudaError_t launch_attention_ref(const __half * qkv, const int32_t * cu_seqlens, int n_sent, int max_len,
+                                 int n_head, int d_head, __half * out, int fq_type, cudaStream_t st);
+
+// K4: masked mean over the sentence's tokens + L2 normalise -> f32 [n_sent][H]
+cudaError_t launch_pool_norm(const __half * x, const int32_t * cu_seqlens, int n_sent, int H,
+                             float * out, cudaStream_t st);
+
+// upload-time transforms (device side)
+cudaError_t launch_f32_to_f16(const float * in, __half * out, size_t n, cudaStream_t st);
+cudaError_t launch_repack_q4(const uint8_t * raw, int type, int N, int K,
+                             uint4 * qnib, __half * qd, __half * qm, cudaStream_t st);
+cudaError_t launch_split_q4_table(const uint8_t * raw, int type, int rows, int H,
+                                  uint4 * qnib, __half * qd, __half * qm, cudaStream_t st);
+cudaError_t launch_dequant_q4_f32(const DevWeight & w, float * out /*[N][K]*/, cudaStream_t st);
+
+// TMA map helper (host): 2-D fp16 row-major [rows][cols], box {64 cols, box_rows}, 128B swizzle
+bool make_tmap_f16_2d(CUtensorMap * map, const void * base, uint64_t rows, uint64_t cols, uint32_t box_rows);
+
+// shared by kernels: q8 fake-quant of 32 consecutive values held by one thread
+__device__ __forceinline__ void fake_quant32(float (&v)[32], int fq_type) {
+    float amax = 0.f;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) amax = fmaxf(amax, fabsf(v[i]));
+    // reference ggml.c:1146-1300 (q8_0) / 1425-1480 (q8_1): d = amax/127, id = 127/amax, rint
+    const float d  = amax / 127.f;
+    const float id = amax != 0.f ? 127.f / amax : 0.f;
+    const float dd = fq_type == W_Q4_0 ? __half2float(__float2half_rn(d)) : d;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = rintf(v[i] * id) * dd;
+}
+
+}  // namespace b200

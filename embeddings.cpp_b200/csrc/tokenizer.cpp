@@ -1,0 +1,166 @@
+#include "tokenizer.h"
+
+#include <cstring>
+
+namespace b200 {
+
+namespace {
+
+constexpr int32_t kCls = 101, kSep = 102, kUnk = 100;
+
+// bert.cpp:199-204 -- length from the lead byte's high nibble (continuation bytes count as 1)
+inline size_t utf8_len(unsigned char c) {
+    static const uint8_t lut[16] = {1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 2, 2, 3, 4};
+    return lut[c >> 4];
+}
+
+// bert.cpp:209-219 -- the 52 Latin-1 letters (all are 0xC3 0x80..0xBF in UTF-8); 0 = not mapped
+inline char accent_fold(unsigned char b0, unsigned char b1) {
+    if (b0 != 0xC3) return 0;
+    static const char * map =
+        /* 0x80 */ "AAAAAA\0CEEEEIIII"
+        /* 0x90 */ "\0NOOOOO\0\0UUUUY\0\0"
+        /* 0xA0 */ "aaaaaa\0ceeeeiiii"
+        /* 0xB0 */ "\0nooooo\0\0uuuuy\0\0";
+    if (b1 < 0x80 || b1 > 0xBF) return 0;
+    return map[b1 - 0x80];
+}
+
+// C-locale ispunct / isspace on a (possibly negative) char: bytes >= 0x80 are neither
+inline bool is_punct(unsigned char c) {
+    return (c >= 33 && c <= 47) || (c >= 58 && c <= 64) || (c >= 91 && c <= 96) || (c >= 123 && c <= 126);
+}
+inline bool is_space(unsigned char c) { return c == ' ' || (c >= 9 && c <= 13); }
+
+// bert.cpp:253-295 on the (up to) 3 bytes at p; `avail` bytes are readable
+inline bool is_chinese3(const unsigned char * p, size_t avail) {
+    // caller guarantees utf8_len(p[0]) == 3, i.e. p[0] in 0xE0..0xEF
+    uint32_t cp = p[0] & 0x0F;
+    for (int j = 1; j < 3; ++j) {
+        if ((size_t) j >= avail) return false;
+        if ((p[j] >> 6) != 0x02) return false;
+        cp = (cp << 6) | (p[j] & 0x3F);
+    }
+    return (cp >= 0x4E00 && cp <= 0x9FFF) || (cp >= 0x3400 && cp <= 0x4DBF) || (cp >= 0xF900 && cp <= 0xFAFF) ||
+           (cp >= 0x3000 && cp <= 0x303F) || (cp >= 0xFF00 && cp <= 0xFFEF);
+    // the supplementary-plane ranges of bert.cpp:284-289 cannot be reached by a 3-byte sequence
+}
+
+}  // namespace
+
+void Tokenizer::build(std::vector<std::string> && vocab) {
+    vocab_ = std::move(vocab);
+    token_to_id_.clear();
+    subword_to_id_.clear();
+    token_to_id_.reserve(vocab_.size() * 2);
+    subword_to_id_.reserve(vocab_.size());
+    id_in_token_map_.assign(vocab_.size(), 0);
+    max_tok_len_ = max_sub_len_ = 0;
+    for (size_t i = 0; i < vocab_.size(); ++i) {
+        const std::string & w = vocab_[i];
+        if (w.size() >= 2 && w[0] == '#' && w[1] == '#') {
+            std::string_view sub(w.data() + 2, w.size() - 2);
+            subword_to_id_[sub] = (int32_t) i;                       // operator[] = : last wins
+            if (sub.size() > max_sub_len_) max_sub_len_ = sub.size();
+        }
+        std::string_view key(w);
+        if (token_to_id_.find(key) == token_to_id_.end()) {          // count()==0 : first wins
+            token_to_id_.emplace(key, (int32_t) i);
+            id_in_token_map_[i] = 1;
+            if (key.size() > max_tok_len_) max_tok_len_ = key.size();
+        }
+    }
+}
+
+const char * Tokenizer::id_to_token(int32_t id) const {
+    if (id >= 0 && (size_t) id < vocab_.size()) {
+        const std::string & w = vocab_[id];
+        if (id_in_token_map_[id]) return w.c_str();
+        if (w.size() >= 2 && w[0] == '#' && w[1] == '#') return w.c_str();
+    }
+    return "[UNK TOKEN from bert_vocab]";
+}
+
+int32_t Tokenizer::tokenize(const char * text, int32_t * out, int32_t n_max) const {
+    if (n_max <= 0) return 0;
+    const size_t len = strlen(text);
+    const unsigned char * src = reinterpret_cast<const unsigned char *>(text);
+
+    // 1. stripAccents (bert.cpp:221-235): walk by utf8_len, fold the 52 mapped letters
+    std::string s;
+    s.reserve(len + 8);
+    for (size_t i = 0; i < len;) {
+        const size_t n = utf8_len(src[i]);
+        if (n == 2 && i + 1 < len) {
+            const char a = accent_fold(src[i], src[i + 1]);
+            if (a) { s.push_back(a); i += 2; continue; }
+        }
+        const size_t take = i + n <= len ? n : len - i;               // substr clips at the end
+        s.append(text + i, take);
+        i += n;
+    }
+    // 2. ASCII lower-casing at character starts only (bert.cpp:244-249)
+    for (size_t i = 0; i < s.size(); i += utf8_len((unsigned char) s[i])) {
+        const char c = s[i];
+        if (c >= 'A' && c <= 'Z') s[i] = (char) (c - 'A' + 'a');
+    }
+    // 3. isolate ASCII punctuation and 3-byte CJK with spaces, byte-wise (bert.cpp:317-339)
+    std::string t;
+    t.reserve(s.size() * 2 + 8);
+    const unsigned char * p = reinterpret_cast<const unsigned char *>(s.data());
+    for (size_t i = 0; i < s.size();) {
+        const size_t n = utf8_len(p[i]);
+        if (n == 1 && is_punct(p[i])) {
+            t.push_back(' '); t.push_back((char) p[i]); t.push_back(' ');
+            i += 1;
+        } else if (n == 3 && is_chinese3(p + i, s.size() - i)) {
+            t.push_back(' '); t.append(s, i, 3); t.push_back(' ');
+            i += 3;
+        } else {
+            t.push_back((char) p[i]);
+            i += 1;
+        }
+    }
+    // 4 + 5. split on isspace, greedy longest match per word (bert.cpp:341-416)
+    int32_t nt = 0;
+    out[nt++] = kCls;
+    if (n_max == 1) return nt;                                        // no room even for [SEP]
+    const char * tb = t.data();
+    const size_t tl = t.size();
+    size_t l = 0;
+    while (l < tl) {
+        while (l < tl && is_space((unsigned char) tb[l])) ++l;
+        size_t r = l;
+        while (r < tl && !is_space((unsigned char) tb[r])) ++r;
+        if (r == l) break;
+        const char * w = tb + l;
+        const size_t n = r - l;
+        l = r;
+        const int32_t prev = nt;
+        size_t i = 0;
+        const std::unordered_map<std::string_view, int32_t> * map = &token_to_id_;
+        size_t maxlen = max_tok_len_;
+        while (i < n) {
+            if (nt >= n_max - 1) break;
+            size_t j = n - i > maxlen ? i + maxlen : n;               // longer pieces cannot match
+            bool found = false;
+            for (; j > i; --j) {
+                auto it = map->find(std::string_view(w + i, j - i));
+                if (it != map->end()) {
+                    out[nt++] = it->second;
+                    i = j;
+                    found = true;
+                    break;
+                }
+            }
+            if (!found) ++i;                                          // skip ONE byte (bert.cpp:401-406)
+            map = &subword_to_id_;
+            maxlen = max_sub_len_;
+        }
+        if (prev == nt && nt < n_max - 1) out[nt++] = kUnk;           // bounded, unlike bert.cpp:408-412
+    }
+    out[nt++] = kSep;
+    return nt;
+}
+
+}  // namespace b200

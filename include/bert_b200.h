@@ -1,0 +1,65 @@
+/*
+ * bert_b200.h -- extension entry points of libbert.so beyond the reference ABI (bert.h).
+ *
+ * Plain C ABI (pointers and sizes only).  These exist for measurement and kernel-level
+ * parity tests; a consumer of the reference never needs them.  The reference has no
+ * counterpart except where cited.
+ */
+#ifndef BERT_B200_H
+#define BERT_B200_H
+
+#include "bert.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Number of GPUs this context holds a weight replica on (BERT_CUDA_DEVICES / all visible). */
+BERT_API int32_t bertx_n_devices(struct bert_ctx * ctx);
+
+/* Model header fields (reference bert.cpp:453-459), index: 0 n_vocab, 1 n_max_tokens,
+ * 2 n_embd, 3 n_intermediate, 4 n_head, 5 n_layer, 6 ftype. */
+BERT_API int32_t bertx_hparam(struct bert_ctx * ctx, int32_t index);
+
+/* Tokenise n_inputs texts with the host tokenizer (threaded); ids are written packed
+ * back-to-back into tokens_out (capacity cap ids), lengths into n_tokens_out.
+ * Returns total ids written or -1 if cap is too small.  Same ids as bert_tokenize. */
+BERT_API int64_t bertx_tokenize_batch(struct bert_ctx * ctx, int32_t n_threads, int32_t n_inputs,
+                                      const char ** texts, bert_vocab_id * tokens_out, int64_t cap,
+                                      int32_t * n_tokens_out);
+
+/* Stage a whole job on device `dev` (index into the context's device list): packed ids
+ * + lengths are copied to HBM and cut into micro-batches.  Returns 0 on success. */
+BERT_API int32_t bertx_stage(struct bert_ctx * ctx, int32_t dev, int32_t n_sent,
+                             const bert_vocab_id * tokens_packed, const int32_t * n_tokens);
+
+/* Run the encoder forward over the staged job `reps` times with inputs already resident
+ * in HBM.  The timed region (CUDA events on the launch stream) covers all kernels of all
+ * micro-batches; *ms_total receives the elapsed milliseconds for all reps.  If out is
+ * non-NULL the [n_sent, n_embd] f32 embeddings of the last rep are copied to it afterwards
+ * (outside the timed region), in staging order.  Returns 0 on success. */
+BERT_API int32_t bertx_run_staged(struct bert_ctx * ctx, int32_t dev, int32_t reps,
+                                  float * ms_total, float * out);
+
+/* Same job, but every kernel class is bracketed by its own events (serialised):
+ * ms_by_kind[k] = total ms, launches_by_kind[k] = launch count, for k in
+ * 0 embed_ln, 1 gemm, 2 attention, 3 add_ln, 4 pool_norm, 5 other.  Arrays of 8. */
+BERT_API int32_t bertx_profile_staged(struct bert_ctx * ctx, int32_t dev,
+                                      float * ms_by_kind, int64_t * launches_by_kind);
+
+/* Kernel launches issued by this context since load (all devices). */
+BERT_API int64_t bertx_kernel_launches(struct bert_ctx * ctx);
+
+/* Kernel self-tests: run the production kernel and a simple SIMT reference kernel on the
+ * same random device data and report the largest absolute difference and the largest
+ * reference magnitude.  wtype: 1 f16, 2 q4_0, 3 q4_1.  epilogue bit0 bias, bit1 GELU,
+ * bit2 residual, bit3 q8 fake-quant of the output.  Return 0 on success (ran), <0 error. */
+BERT_API int32_t bertx_selftest_gemm(int32_t M, int32_t N, int32_t K, int32_t wtype, int32_t epilogue,
+                                     int32_t seed, float * max_abs_err, float * max_ref);
+BERT_API int32_t bertx_selftest_attention(int32_t n_sent, int32_t max_len, int32_t n_head, int32_t d_head,
+                                          int32_t seed, float * max_abs_err, float * max_ref);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BERT_B200_H */
