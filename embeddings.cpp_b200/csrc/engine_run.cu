@@ -1,0 +1,199 @@
+// The encoder forward as a fixed sequence of sm_100a kernels on one stream per GPU, and
+// the host scheduler that feeds it (length sort, token-budget micro-batches, sharding of
+// micro-batches over the GPUs with no collective, pinned double-buffered staging).
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <numeric>
+#include <thread>
+
+#include "engine.h"
+
+namespace b200 {
+
+namespace {
+
+struct Launcher {
+    Engine & e; Replica & r; bool ok = true;
+    void operator()(int kind, cudaError_t err, const char * what) {
+        e.launches.fetch_add(1, std::memory_order_relaxed);
+        (void) kind;
+        if (err != cudaSuccess) { ok = false; cuda_ok(err, what); }
+    }
+};
+
+}  // namespace
+
+// One micro-batch.  Kernel sequence per layer (reference graph nodes in brackets):
+//   GEMM qkv  [bert.cpp:993-1016]  ->  attention [957-961, 1018-1036]  ->  GEMM o + bias +
+//   residual [1040-1045]  ->  LN [1047-1056]  ->  GEMM ffn-in + bias + GELU [1059-1063]  ->
+//   GEMM ffn-out + bias + residual [1066-1071]  ->  LN [1073-1082]
+bool Engine::forward(Replica & r, const int32_t * d_ids, const int32_t * d_cu, int n_sent, int T, int max_len,
+                     float * d_out) {
+    const int H = hp.n_embd;
+    const bool fq = fq_type >= 0;
+    cudaStream_t st = r.stream;
+    Launcher L{*this, r};
+
+    auto begin = [&](int kind) {
+        if (!r.profiling) return;
+        Replica::Span s; s.kind = kind;
+        cudaEventCreate(&s.a); cudaEventCreate(&s.b);
+        cudaEventRecord(s.a, st);
+        r.spans.push_back(s);
+    };
+    auto end = [&]() { if (r.profiling) cudaEventRecord(r.spans.back().b, st); };
+
+    auto gemm = [&](const CUtensorMap * tm, const __half * a, const DevWeight & w, const __half * res, __half * out,
+                    int epi) {
+        GemmArgs g{tm, a, &w, res, out, T, epi, fq_type};
+        begin(KK_GEMM);
+        L(KK_GEMM, gemm_simt ? launch_gemm_simt(g, st) : launch_gemm_tc(g, r.num_sms, st), "gemm");
+        end();
+    };
+
+    begin(KK_EMBED);
+    L(KK_EMBED, launch_embed_ln(r.word, r.postype, r.ln_e_g, r.ln_e_b, d_ids, d_cu, n_sent, T, H,
+                                r.x, fq ? r.xq : nullptr, fq_type, st), "embed_ln");
+    end();
+    for (int il = 0; il < hp.n_layer && L.ok; ++il) {
+        const LayerDev & ly = r.layers[il];
+        gemm(&r.tm_xin, r.xq, ly.qkv, nullptr, r.qkv, EPI_BIAS);
+        begin(KK_ATTN);
+        L(KK_ATTN, (attn_ref ? launch_attention_ref : launch_attention)(r.qkv, d_cu, n_sent, max_len, hp.n_head,
+                                                                         H / hp.n_head, r.ctx, fq_type, st), "attention");
+        end();
+        gemm(&r.tm_ctx, r.ctx, ly.o, r.x, r.y, EPI_BIAS | EPI_RESIDUAL);
+        begin(KK_LN);
+        L(KK_LN, launch_ln(r.y, ly.ln_att_g, ly.ln_att_b, T, H, r.x1, fq ? r.x1q : nullptr, fq_type, st), "ln_att");
+        end();
+        gemm(&r.tm_x1in, r.x1q, ly.ffi, nullptr, r.mid, EPI_BIAS | EPI_GELU | (fq ? EPI_FAKEQUANT : 0));
+        gemm(&r.tm_mid, r.mid, ly.ffo, r.x1, r.y, EPI_BIAS | EPI_RESIDUAL);
+        begin(KK_LN);
+        L(KK_LN, launch_ln(r.y, ly.ln_out_g, ly.ln_out_b, T, H, r.x, fq ? r.xq : nullptr, fq_type, st), "ln_out");
+        end();
+    }
+    begin(KK_POOL);
+    L(KK_POOL, launch_pool_norm(r.x, d_cu, n_sent, H, d_out, st), "pool_norm");
+    end();
+    return L.ok;
+}
+
+void Engine::plan(const int32_t * n_tokens, int n, std::vector<int> & order, std::vector<MicroBatch> & mbs) const {
+    order.resize(n);
+    std::iota(order.begin(), order.end(), 0);
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return n_tokens[a] > n_tokens[b]; });
+    mbs.clear();
+    MicroBatch cur;
+    size_t off = 0;
+    for (int i = 0; i < n; ++i) {
+        const int len = n_tokens[order[i]];
+        if (cur.count > 0 && (cur.tokens + len > t_cap || cur.count + 1 > b_cap)) {
+            mbs.push_back(cur);
+            cur = MicroBatch();
+            cur.first = i; cur.tok_offset = off;
+        }
+        if (cur.count == 0) { cur.first = i; cur.tok_offset = off; }
+        cur.count++; cur.tokens += len; cur.max_len = std::max(cur.max_len, len);
+        off += len;
+    }
+    if (cur.count > 0) mbs.push_back(cur);
+}
+
+bool Engine::run_on_replica(Replica & r, const std::vector<int> & order, const std::vector<MicroBatch> & mbs,
+                            const std::vector<int> & mine, const int32_t * const * tokens, const int32_t * n_tokens,
+                            float * const * out) {
+    if (!cuda_ok(cudaSetDevice(r.device), "cudaSetDevice")) return false;
+    const int H = hp.n_embd;
+    bool ok = true;
+    int pending[Replica::kSlots] = {-1, -1};          // micro-batch whose results sit in the slot
+    auto drain = [&](int s) {
+        if (pending[s] < 0) return;
+        if (!cuda_ok(cudaEventSynchronize(r.slot_done[s]), "slot sync")) { ok = false; pending[s] = -1; return; }
+        const MicroBatch & mb = mbs[pending[s]];
+        for (int i = 0; i < mb.count; ++i) {
+            memcpy(out[order[mb.first + i]], r.h_out[s] + (size_t) i * H, (size_t) H * sizeof(float));
+        }
+        pending[s] = -1;
+    };
+    for (size_t k = 0; k < mine.size() && ok; ++k) {
+        const int s = (int) (k % Replica::kSlots);
+        drain(s);
+        if (!ok) break;
+        const MicroBatch & mb = mbs[mine[k]];
+        int32_t * ids = r.h_ids[s];
+        int32_t * cu = r.h_cu[s];
+        int t = 0;
+        for (int i = 0; i < mb.count; ++i) {
+            const int idx = order[mb.first + i];
+            cu[i] = t;
+            memcpy(ids + t, tokens[idx], (size_t) n_tokens[idx] * sizeof(int32_t));
+            t += n_tokens[idx];
+        }
+        cu[mb.count] = t;
+        ok = ok && cuda_ok(cudaMemcpyAsync(r.d_ids[s], ids, (size_t) t * 4, cudaMemcpyHostToDevice, r.stream), "H2D ids");
+        ok = ok && cuda_ok(cudaMemcpyAsync(r.d_cu[s], cu, (size_t) (mb.count + 1) * 4, cudaMemcpyHostToDevice, r.stream), "H2D cu");
+        ok = ok && forward(r, r.d_ids[s], r.d_cu[s], mb.count, t, mb.max_len, r.d_out[s]);
+        ok = ok && cuda_ok(cudaMemcpyAsync(r.h_out[s], r.d_out[s], (size_t) mb.count * H * 4, cudaMemcpyDeviceToHost, r.stream), "D2H out");
+        ok = ok && cuda_ok(cudaEventRecord(r.slot_done[s], r.stream), "event record");
+        if (ok) pending[s] = mine[k];
+    }
+    for (int s = 0; s < Replica::kSlots; ++s) drain(s);
+    if (!ok) cudaStreamSynchronize(r.stream);
+    const cudaError_t e = cudaGetLastError();
+    return ok && e == cudaSuccess;
+}
+
+bool Engine::run_tokens(const int32_t * const * tokens, const int32_t * n_tokens, int n, float * const * out) {
+    if (n <= 0) return true;
+    for (int i = 0; i < n; ++i) {
+        if (n_tokens[i] > hp.n_max_tokens) {                  // reference bert.cpp:867-871
+            fprintf(stderr, "Too many tokens, maximum is %d\n", hp.n_max_tokens);
+            return false;
+        }
+        if (n_tokens[i] <= 0) {
+            fprintf(stderr, "bert_forward_batch: input %d has no tokens\n", i);
+            return false;
+        }
+    }
+    std::vector<int> order;
+    std::vector<MicroBatch> mbs;
+    plan(n_tokens, n, order, mbs);
+    const int H = hp.n_embd, I = hp.n_intermediate;
+    // longest-processing-time assignment of micro-batches to GPUs (cost ~ FLOPs)
+    const size_t nd = reps.size();
+    std::vector<std::vector<int>> mine(nd);
+    std::vector<double> load(nd, 0.0);
+    std::vector<int> by_cost(mbs.size());
+    std::iota(by_cost.begin(), by_cost.end(), 0);
+    auto cost = [&](const MicroBatch & m) {
+        return (double) m.tokens * (8.0 * H * H + 4.0 * H * I) + 4.0 * (double) m.tokens * m.max_len * H;
+    };
+    std::stable_sort(by_cost.begin(), by_cost.end(), [&](int a, int b) { return cost(mbs[a]) > cost(mbs[b]); });
+    for (int m : by_cost) {
+        const size_t d = std::min_element(load.begin(), load.end()) - load.begin();
+        mine[d].push_back(m);
+        load[d] += cost(mbs[m]);
+    }
+    // temporaries in a failed call must not leak into caller buffers: results are only
+    // scattered per finished micro-batch; on failure the remaining outputs stay untouched.
+    if (nd == 1) return run_on_replica(reps[0], order, mbs, mine[0], tokens, n_tokens, out);
+    std::vector<std::thread> th;
+    std::vector<char> oks(nd, 1);
+    for (size_t d = 0; d < nd; ++d) {
+        if (mine[d].empty()) continue;
+        th.emplace_back([&, d]() { oks[d] = run_on_replica(reps[d], order, mbs, mine[d], tokens, n_tokens, out) ? 1 : 0; });
+    }
+    for (auto & t : th) t.join();
+    return std::all_of(oks.begin(), oks.end(), [](char c) { return c != 0; });
+}
+
+void Engine::free_job(Replica & r) {
+    if (r.job_ids) cudaFree(r.job_ids);
+    if (r.job_cu) cudaFree(r.job_cu);
+    if (r.job_out) cudaFree(r.job_out);
+    r.job_ids = nullptr; r.job_cu = nullptr; r.job_out = nullptr;
+    r.job_mbs.clear(); r.job_order.clear(); r.job_cu_off.clear(); r.job_sent = 0;
+}
+
+}  // namespace b200

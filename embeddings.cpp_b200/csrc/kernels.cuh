@@ -82,7 +82,8 @@ cudaError_t launch_pool_norm(const __half * x, const int32_t * cu_seqlens, int n
 
 // upload-time transforms (device side)
 cudaError_t launch_f32_to_f16(const float * in, __half * out, size_t n, cudaStream_t st);
-cudaError_t launch_repack_q4(const uint8_t * raw, int type, int N, int K,
+// rows [n_offset, n_offset+N) of a plane set holding N_total rows (lets Q|K|V share one GEMM)
+cudaError_t launch_repack_q4(const uint8_t * raw, int type, int N, int K, int n_offset, int N_total,
                              uint4 * qnib, __half * qd, __half * qm, cudaStream_t st);
 cudaError_t launch_split_q4_table(const uint8_t * raw, int type, int rows, int H,
                                   uint4 * qnib, __half * qd, __half * qm, cudaStream_t st);

@@ -32,7 +32,7 @@ __device__ __forceinline__ void read_block(const uint8_t * raw, int type, size_t
 //   element 8k+2i   at bits [4i, 4i+4),  element 8k+2i+1 at bits [16+4i, 16+4i+4)
 // so that ((w >> 4i) & 0x000F000F) | 0x64006400 is the fp16 pair (1024+e, 1024+e') of two
 // ADJACENT weights (see dq_pair in gemm_tc.cu).
-__global__ void repack_q4_kernel(const uint8_t * __restrict__ raw, int type, int N, int K,
+__global__ void repack_q4_kernel(const uint8_t * __restrict__ raw, int type, int N, int K, int n_offset, int N_total,
                                  uint4 * __restrict__ qnib, __half * __restrict__ qd, __half * __restrict__ qm) {
     const size_t nblk = (size_t) N * (K / 32);
     const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
@@ -52,7 +52,7 @@ __global__ void repack_q4_kernel(const uint8_t * __restrict__ raw, int type, int
         for (int q = 0; q < 4; ++q) x |= (e[8 * k + 2 * q] << (4 * q)) | (e[8 * k + 2 * q + 1] << (16 + 4 * q));
         w[k] = x;
     }
-    const size_t dst = ((size_t) (kb32 >> 1) * N + n) * 2 + (kb32 & 1);       // [K/64][N][2]
+    const size_t dst = ((size_t) (kb32 >> 1) * N_total + n_offset + n) * 2 + (kb32 & 1);       // [K/64][N_total][2]
     qnib[dst] = make_uint4(w[0], w[1], w[2], w[3]);
     qd[dst] = __ushort_as_half(d);
     if (type == W_Q4_1) qm[dst] = __ushort_as_half(m);
@@ -179,10 +179,10 @@ cudaError_t launch_f32_to_f16(const float * in, __half * out, size_t n, cudaStre
     return cudaGetLastError();
 }
 
-cudaError_t launch_repack_q4(const uint8_t * raw, int type, int N, int K,
+cudaError_t launch_repack_q4(const uint8_t * raw, int type, int N, int K, int n_offset, int N_total,
                              uint4 * qnib, __half * qd, __half * qm, cudaStream_t st) {
     const size_t nblk = (size_t) N * (K / 32);
-    repack_q4_kernel<<<(unsigned) ((nblk + 127) / 128), 128, 0, st>>>(raw, type, N, K, qnib, qd, qm);
+    repack_q4_kernel<<<(unsigned) ((nblk + 127) / 128), 128, 0, st>>>(raw, type, N, K, n_offset, N_total, qnib, qd, qm);
     return cudaGetLastError();
 }
 
