@@ -1,0 +1,206 @@
+"""embeddings.cpp_b200 -- B200-native BERT embedding engine behind the reference's bert.h ABI.
+
+The product is ``lib/libbert.so`` (hand-written CUDA for sm_100a + C++ host runtime, built
+by ``build.py``).  This module is the Python mirror of the reference's ctypes consumer
+(/root/reference/examples/sample_dylib.py:15-62, benchmarks/run_mteb.py:34-83): the same
+``BertModel(fname).encode(sentences, batch_size)`` surface bound to the same C symbols.
+There is no CPU fallback: loading fails loudly when the library or a B200 is missing.
+
+The directory name contains a dot, so import it through the ``load_package()`` helper in
+``__graft_entry__.py`` (importlib by path) rather than ``import embeddings.cpp_b200``.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "lib", "libbert.so")
+
+_lib = None
+
+
+def build(force=False):
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("_b200_build", os.path.join(HERE, "build.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod.build(force=force)
+
+
+def lib():
+    """The loaded C-ABI library with argtypes set (raises if it has not been built)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} is missing: run `python embeddings.cpp_b200/build.py` "
+                           "(there is no fallback implementation)")
+    L = ctypes.cdll.LoadLibrary(LIB_PATH)
+    c_i32, c_i64, vp, cp = ctypes.c_int32, ctypes.c_int64, ctypes.c_void_p, ctypes.c_char_p
+    pf, pi = ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_int32)
+    L.bert_load_from_file.restype = vp
+    L.bert_load_from_file.argtypes = [cp]
+    L.bertx_load_host_only.restype = vp
+    L.bertx_load_host_only.argtypes = [cp]
+    L.bert_free.argtypes = [vp]
+    L.bert_n_embd.restype = c_i32
+    L.bert_n_embd.argtypes = [vp]
+    L.bert_n_max_tokens.restype = c_i32
+    L.bert_n_max_tokens.argtypes = [vp]
+    L.bert_vocab_id_to_token.restype = cp
+    L.bert_vocab_id_to_token.argtypes = [vp, c_i32]
+    L.bert_encode.argtypes = [vp, c_i32, cp, pf]
+    L.bert_encode_batch.argtypes = [vp, c_i32, c_i32, c_i32, ctypes.POINTER(cp), ctypes.POINTER(pf)]
+    L.bert_tokenize.argtypes = [vp, cp, pi, pi, c_i32]
+    L.bert_forward.argtypes = [vp, c_i32, pi, c_i32, pf]
+    L.bert_forward_batch.argtypes = [vp, c_i32, c_i32, ctypes.POINTER(pi), pi, ctypes.POINTER(pf)]
+    L.bert_forward_fake_batch.argtypes = L.bert_forward_batch.argtypes
+    L.bertx_n_devices.restype = c_i32
+    L.bertx_n_devices.argtypes = [vp]
+    L.bertx_hparam.restype = c_i32
+    L.bertx_hparam.argtypes = [vp, c_i32]
+    L.bertx_kernel_launches.restype = c_i64
+    L.bertx_kernel_launches.argtypes = [vp]
+    L.bertx_tokenize_batch.restype = c_i64
+    L.bertx_tokenize_batch.argtypes = [vp, c_i32, c_i32, ctypes.POINTER(cp), pi, c_i64, pi]
+    L.bertx_stage.restype = c_i32
+    L.bertx_stage.argtypes = [vp, c_i32, c_i32, pi, pi]
+    L.bertx_run_staged.restype = c_i32
+    L.bertx_run_staged.argtypes = [vp, c_i32, c_i32, pf, pf]
+    L.bertx_profile_staged.restype = c_i32
+    L.bertx_profile_staged.argtypes = [vp, c_i32, pf, ctypes.POINTER(c_i64)]
+    L.bertx_selftest_gemm.restype = c_i32
+    L.bertx_selftest_gemm.argtypes = [c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, pf, pf]
+    L.bertx_selftest_attention.restype = c_i32
+    L.bertx_selftest_attention.argtypes = [c_i32, c_i32, c_i32, c_i32, c_i32, pf, pf]
+    _lib = L
+    return L
+
+
+def _fp(a):
+    return a.ctypes.data_as(ctypes.POINTER(ctypes.c_float))
+
+
+def _ip(a):
+    return a.ctypes.data_as(ctypes.POINTER(ctypes.c_int32))
+
+
+class BertModel:
+    """Same surface as the reference's examples/sample_dylib.py BertModel."""
+
+    def __init__(self, fname, host_only=False, n_threads=None):
+        self.lib = lib()
+        fn = fname.encode() if isinstance(fname, str) else fname
+        self.ctx = (self.lib.bertx_load_host_only if host_only else self.lib.bert_load_from_file)(fn)
+        if not self.ctx:
+            raise RuntimeError(f"bert_load_from_file('{fname}') failed (see stderr)")
+        self.n_embd = self.lib.bert_n_embd(self.ctx)
+        self.n_max_tokens = self.lib.bert_n_max_tokens(self.ctx)
+        self.n_threads = n_threads or min(os.cpu_count() or 1, 32)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def close(self):
+        if getattr(self, "ctx", None):
+            self.lib.bert_free(self.ctx)
+            self.ctx = None
+
+    # -- reference surface -----------------------------------------------------------
+    def encode(self, sentences, batch_size=16):
+        """bert_encode_batch; returns [n, n_embd] float32 (sample_dylib.py:42-62)."""
+        n = len(sentences)
+        out = np.zeros((n, self.n_embd), dtype=np.float32)
+        if n == 0:
+            return out
+        texts = (ctypes.c_char_p * n)(*[s if isinstance(s, bytes) else s.encode("utf-8") for s in sentences])
+        rows = (ctypes.POINTER(ctypes.c_float) * n)(*[_fp(out[i]) for i in range(n)])
+        self.lib.bert_encode_batch(self.ctx, self.n_threads, batch_size, n, texts, rows)
+        return out
+
+    def tokenize(self, text, n_max=None):
+        n_max = self.n_max_tokens if n_max is None else n_max
+        buf = np.zeros(max(n_max, 1) + 8, dtype=np.int32)
+        n = ctypes.c_int32(0)
+        self.lib.bert_tokenize(self.ctx, text if isinstance(text, bytes) else text.encode("utf-8"),
+                               _ip(buf), ctypes.byref(n), n_max)
+        return buf[:n.value].tolist()
+
+    def id_to_token(self, i):
+        return self.lib.bert_vocab_id_to_token(self.ctx, i)
+
+    def forward_tokens(self, batch_tokens, fake_batch=False):
+        """bert_forward_batch on lists of ids; returns [n, n_embd] float32."""
+        n = len(batch_tokens)
+        out = np.zeros((n, self.n_embd), dtype=np.float32)
+        arrs = [np.ascontiguousarray(t, dtype=np.int32) for t in batch_tokens]
+        ptrs = (ctypes.POINTER(ctypes.c_int32) * n)(*[_ip(a) for a in arrs])
+        lens = np.array([len(a) for a in arrs], dtype=np.int32)
+        rows = (ctypes.POINTER(ctypes.c_float) * n)(*[_fp(out[i]) for i in range(n)])
+        fn = self.lib.bert_forward_fake_batch if fake_batch else self.lib.bert_forward_batch
+        fn(self.ctx, self.n_threads, n, ptrs, _ip(lens), rows)
+        return out
+
+    # -- measurement extensions (bert_b200.h) -----------------------------------------
+    def n_devices(self):
+        return self.lib.bertx_n_devices(self.ctx)
+
+    def hparams(self):
+        k = ["n_vocab", "n_max_tokens", "n_embd", "n_intermediate", "n_head", "n_layer", "ftype"]
+        return {name: self.lib.bertx_hparam(self.ctx, i) for i, name in enumerate(k)}
+
+    def kernel_launches(self):
+        return int(self.lib.bertx_kernel_launches(self.ctx))
+
+    def tokenize_batch(self, sentences):
+        n = len(sentences)
+        texts = (ctypes.c_char_p * n)(*[s if isinstance(s, bytes) else s.encode("utf-8") for s in sentences])
+        cap = n * self.n_max_tokens
+        ids = np.zeros(cap, dtype=np.int32)
+        lens = np.zeros(n, dtype=np.int32)
+        tot = self.lib.bertx_tokenize_batch(self.ctx, self.n_threads, n, texts, _ip(ids), cap, _ip(lens))
+        if tot < 0:
+            raise RuntimeError("bertx_tokenize_batch failed")
+        return ids[:tot].copy(), lens
+
+    def stage(self, ids, lens, dev=0):
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        lens = np.ascontiguousarray(lens, dtype=np.int32)
+        rc = self.lib.bertx_stage(self.ctx, dev, len(lens), _ip(ids), _ip(lens))
+        if rc != 0:
+            raise RuntimeError(f"bertx_stage failed ({rc})")
+        self._staged = len(lens)
+
+    def run_staged(self, reps=1, dev=0, fetch=False):
+        """Returns (milliseconds for all reps, embeddings or None)."""
+        ms = ctypes.c_float(0)
+        out = np.zeros((self._staged, self.n_embd), dtype=np.float32) if fetch else None
+        rc = self.lib.bertx_run_staged(self.ctx, dev, reps, ctypes.byref(ms), _fp(out) if fetch else None)
+        if rc != 0:
+            raise RuntimeError(f"bertx_run_staged failed ({rc})")
+        return ms.value, out
+
+    def profile_staged(self, dev=0):
+        ms = np.zeros(8, dtype=np.float32)
+        cnt = np.zeros(8, dtype=np.int64)
+        rc = self.lib.bertx_profile_staged(self.ctx, dev, _fp(ms), cnt.ctypes.data_as(ctypes.POINTER(ctypes.c_int64)))
+        if rc != 0:
+            raise RuntimeError(f"bertx_profile_staged failed ({rc})")
+        names = ["embed_ln", "gemm", "attention", "add_ln", "pool_norm", "other"]
+        return {n: (float(ms[i]), int(cnt[i])) for i, n in enumerate(names)}
+
+
+def selftest_gemm(M, N, K, wtype, epilogue, seed=0):
+    err, ref = ctypes.c_float(0), ctypes.c_float(0)
+    rc = lib().bertx_selftest_gemm(M, N, K, wtype, epilogue, seed, ctypes.byref(err), ctypes.byref(ref))
+    return rc, err.value, ref.value
+
+
+def selftest_attention(n_sent, max_len, n_head, d_head, seed=0):
+    err, ref = ctypes.c_float(0), ctypes.c_float(0)
+    rc = lib().bertx_selftest_attention(n_sent, max_len, n_head, d_head, seed, ctypes.byref(err), ctypes.byref(ref))
+    return rc, err.value, ref.value

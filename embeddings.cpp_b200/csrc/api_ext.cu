@@ -1,0 +1,237 @@
+// Measurement entry points (bert_b200.h): device-resident jobs timed with CUDA events on
+// the launch stream, per-kernel-class profiling, and the kernel self-tests.
+#include <cstdio>
+#include <cstring>
+#include <random>
+#include <vector>
+
+#include "../../include/bert_b200.h"
+#include "engine.h"
+
+using namespace b200;
+
+extern "C" {
+
+int32_t bertx_stage(struct bert_ctx * ctx, int32_t dev, int32_t n_sent, const bert_vocab_id * tokens_packed,
+                    const int32_t * n_tokens) {
+    Engine & e = ctx->eng;
+    if (dev < 0 || dev >= (int) e.reps.size() || n_sent <= 0) return -1;
+    std::lock_guard<std::mutex> lock(e.mu);
+    Replica & r = e.reps[dev];
+    if (!cuda_ok(cudaSetDevice(r.device), "cudaSetDevice")) return -2;
+    cudaStreamSynchronize(r.stream);
+    e.free_job(r);
+    for (int i = 0; i < n_sent; ++i) if (n_tokens[i] <= 0 || n_tokens[i] > e.hp.n_max_tokens) return -3;
+    e.plan(n_tokens, n_sent, r.job_order, r.job_mbs);
+    std::vector<size_t> src_off(n_sent + 1, 0);
+    for (int i = 0; i < n_sent; ++i) src_off[i + 1] = src_off[i] + (size_t) n_tokens[i];
+    std::vector<int32_t> ids(src_off[n_sent]);
+    std::vector<int32_t> cu;
+    r.job_cu_off.clear();
+    size_t t = 0;
+    for (const MicroBatch & mb : r.job_mbs) {
+        r.job_cu_off.push_back(cu.size());
+        int local = 0;
+        for (int i = 0; i < mb.count; ++i) {
+            const int idx = r.job_order[mb.first + i];
+            cu.push_back(local);
+            memcpy(ids.data() + t, tokens_packed + src_off[idx], (size_t) n_tokens[idx] * 4);
+            t += n_tokens[idx]; local += n_tokens[idx];
+        }
+        cu.push_back(local);
+    }
+    if (!cuda_ok(cudaMalloc((void **) &r.job_ids, ids.size() * 4 + 256), "cudaMalloc job ids")) return -4;
+    if (!cuda_ok(cudaMalloc((void **) &r.job_cu, cu.size() * 4 + 256), "cudaMalloc job cu")) return -4;
+    if (!cuda_ok(cudaMalloc((void **) &r.job_out, (size_t) n_sent * e.hp.n_embd * 4 + 256), "cudaMalloc job out")) return -4;
+    if (!cuda_ok(cudaMemcpy(r.job_ids, ids.data(), ids.size() * 4, cudaMemcpyHostToDevice), "H2D job ids")) return -5;
+    if (!cuda_ok(cudaMemcpy(r.job_cu, cu.data(), cu.size() * 4, cudaMemcpyHostToDevice), "H2D job cu")) return -5;
+    r.job_sent = n_sent;
+    return 0;
+}
+
+static bool run_job_once(Engine & e, Replica & r) {
+    for (size_t k = 0; k < r.job_mbs.size(); ++k) {
+        const MicroBatch & mb = r.job_mbs[k];
+        if (!e.forward(r, r.job_ids + mb.tok_offset, r.job_cu + r.job_cu_off[k], mb.count, mb.tokens, mb.max_len,
+                       r.job_out + (size_t) mb.first * e.hp.n_embd)) return false;
+    }
+    return true;
+}
+
+static int32_t copy_job_out(Engine & e, Replica & r, float * out) {
+    const int H = e.hp.n_embd;
+    std::vector<float> tmp((size_t) r.job_sent * H);
+    if (!cuda_ok(cudaMemcpy(tmp.data(), r.job_out, tmp.size() * 4, cudaMemcpyDeviceToHost), "D2H job out")) return -8;
+    for (int i = 0; i < r.job_sent; ++i) memcpy(out + (size_t) r.job_order[i] * H, tmp.data() + (size_t) i * H, (size_t) H * 4);
+    return 0;
+}
+
+int32_t bertx_run_staged(struct bert_ctx * ctx, int32_t dev, int32_t reps, float * ms_total, float * out) {
+    Engine & e = ctx->eng;
+    if (dev < 0 || dev >= (int) e.reps.size() || reps <= 0) return -1;
+    std::lock_guard<std::mutex> lock(e.mu);
+    Replica & r = e.reps[dev];
+    if (r.job_sent <= 0) return -2;
+    if (!cuda_ok(cudaSetDevice(r.device), "cudaSetDevice")) return -3;
+    cudaEvent_t a, b;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    bool ok = cuda_ok(cudaStreamSynchronize(r.stream), "pre sync");
+    cudaEventRecord(a, r.stream);
+    for (int i = 0; i < reps && ok; ++i) ok = run_job_once(e, r);
+    cudaEventRecord(b, r.stream);
+    ok = cuda_ok(cudaStreamSynchronize(r.stream), "run_staged sync") && ok;
+    float ms = 0.f;
+    if (ok) cudaEventElapsedTime(&ms, a, b);
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    if (ms_total) *ms_total = ms;
+    if (!ok) return -7;
+    if (out) return copy_job_out(e, r, out);
+    return 0;
+}
+
+int32_t bertx_profile_staged(struct bert_ctx * ctx, int32_t dev, float * ms_by_kind, int64_t * launches_by_kind) {
+    Engine & e = ctx->eng;
+    if (dev < 0 || dev >= (int) e.reps.size()) return -1;
+    std::lock_guard<std::mutex> lock(e.mu);
+    Replica & r = e.reps[dev];
+    if (r.job_sent <= 0) return -2;
+    if (!cuda_ok(cudaSetDevice(r.device), "cudaSetDevice")) return -3;
+    for (int k = 0; k < KK_COUNT; ++k) { ms_by_kind[k] = 0.f; launches_by_kind[k] = 0; }
+    r.profiling = true;
+    const bool ran = run_job_once(e, r);
+    r.profiling = false;
+    const bool ok = cuda_ok(cudaStreamSynchronize(r.stream), "profile sync") && ran;
+    for (Replica::Span & s : r.spans) {
+        float ms = 0.f;
+        if (ok && cudaEventElapsedTime(&ms, s.a, s.b) == cudaSuccess) {
+            ms_by_kind[s.kind] += ms;
+            launches_by_kind[s.kind] += 1;
+        }
+        cudaEventDestroy(s.a); cudaEventDestroy(s.b);
+    }
+    r.spans.clear();
+    return ok ? 0 : -7;
+}
+
+// ---------------------------------------------------------------------------- self-tests
+}  // extern "C"
+
+namespace {
+struct DevBuf {
+    void * p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    bool alloc(size_t bytes) { return cudaMalloc(&p, bytes + 256) == cudaSuccess; }
+    template <typename T> T * as() { return (T *) p; }
+};
+uint16_t f2h_bits(float f) { __half h = __float2half_rn(f); uint16_t u; memcpy(&u, &h, 2); return u; }
+
+// compare two fp16 device arrays; returns max |a-b| and max |b|
+bool compare_h(const __half * da, const __half * db, size_t n, float * max_err, float * max_ref) {
+    std::vector<__half> a(n), b(n);
+    if (cudaMemcpy(a.data(), da, n * 2, cudaMemcpyDeviceToHost) != cudaSuccess) return false;
+    if (cudaMemcpy(b.data(), db, n * 2, cudaMemcpyDeviceToHost) != cudaSuccess) return false;
+    float me = 0.f, mr = 0.f;
+    for (size_t i = 0; i < n; ++i) {
+        const float x = __half2float(a[i]), y = __half2float(b[i]);
+        const float d = fabsf(x - y);
+        if (!(d <= me)) me = d;                 // NaN-propagating max
+        if (fabsf(y) > mr) mr = fabsf(y);
+    }
+    *max_err = me; *max_ref = mr;
+    return true;
+}
+}  // namespace
+
+extern "C" {
+
+int32_t bertx_selftest_gemm(int32_t M, int32_t N, int32_t K, int32_t wtype, int32_t epilogue, int32_t seed,
+                            float * max_abs_err, float * max_ref) {
+    if (M <= 0 || N % 64 || K % 64 || wtype < 1 || wtype > 3) return -1;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { fprintf(stderr, "bertx_selftest_gemm: no CUDA device\n"); return -2; }
+    cudaDeviceProp prop; cudaGetDeviceProperties(&prop, 0);
+    std::mt19937 rng((uint32_t) seed);
+    std::normal_distribution<float> nd(0.f, 1.f);
+    const size_t rows = ((size_t) M + 127) / 128 * 128;
+    std::vector<uint16_t> ha(rows * K, 0), hres((size_t) M * N);
+    for (size_t i = 0; i < (size_t) M * K; ++i) ha[i] = f2h_bits(nd(rng));
+    for (auto & v : hres) v = f2h_bits(nd(rng));
+    std::vector<float> hbias(N);
+    for (auto & v : hbias) v = 0.5f * nd(rng);
+    DevBuf a, res, bias, o1, o2, wbuf, nib, qd, qm;
+    if (!a.alloc(ha.size() * 2) || !res.alloc(hres.size() * 2) || !bias.alloc((size_t) N * 4) ||
+        !o1.alloc((size_t) M * N * 2) || !o2.alloc((size_t) M * N * 2)) return -3;
+    cudaMemcpy(a.p, ha.data(), ha.size() * 2, cudaMemcpyHostToDevice);
+    cudaMemcpy(res.p, hres.data(), hres.size() * 2, cudaMemcpyHostToDevice);
+    cudaMemcpy(bias.p, hbias.data(), (size_t) N * 4, cudaMemcpyHostToDevice);
+    cudaMemset(o1.p, 0xFF, (size_t) M * N * 2);
+    DevWeight w;
+    w.N = N; w.K = K; w.type = wtype; w.bias = bias.as<float>(); w.bn = gemm_pick_bn(N);
+    const float wscale = 1.0f / sqrtf((float) K);
+    if (wtype == W_F16) {
+        std::vector<uint16_t> hw((size_t) N * K);
+        for (auto & v : hw) v = f2h_bits(wscale * nd(rng));
+        if (!wbuf.alloc(hw.size() * 2)) return -3;
+        cudaMemcpy(wbuf.p, hw.data(), hw.size() * 2, cudaMemcpyHostToDevice);
+        w.w16 = wbuf.as<__half>();
+        if (!make_tmap_f16_2d(&w.tmap, w.w16, N, K, w.bn)) return -4;
+    } else {
+        // random raw blocks in the FILE layout, repacked by the production upload kernel
+        const int bs = wtype == W_Q4_0 ? 18 : 20;
+        const size_t nblk = (size_t) N * (K / 32);
+        std::vector<uint8_t> raw(nblk * bs);
+        for (size_t b = 0; b < nblk; ++b) {
+            uint8_t * p = raw.data() + b * bs;
+            const uint16_t d = f2h_bits(wscale * (0.05f + fabsf(nd(rng))) / 4.f);
+            memcpy(p, &d, 2);
+            int off = 2;
+            if (wtype == W_Q4_1) { const uint16_t m = f2h_bits(-2.f * wscale * fabsf(nd(rng))); memcpy(p + 2, &m, 2); off = 4; }
+            for (int j = 0; j < 16; ++j) p[off + j] = (uint8_t) (rng() & 0xFF);
+        }
+        if (!wbuf.alloc(raw.size()) || !nib.alloc(nblk * 16) || !qd.alloc(nblk * 2) || !qm.alloc(nblk * 2)) return -3;
+        cudaMemcpy(wbuf.p, raw.data(), raw.size(), cudaMemcpyHostToDevice);
+        if (launch_repack_q4(wbuf.as<uint8_t>(), wtype, N, K, 0, N, nib.as<uint4>(), qd.as<__half>(), qm.as<__half>(), 0) != cudaSuccess) return -5;
+        w.qnib = nib.as<uint4>(); w.qd = qd.as<__half>(); w.qm = wtype == W_Q4_1 ? qm.as<__half>() : nullptr;
+        memset(&w.tmap, 0, sizeof(w.tmap));
+    }
+    CUtensorMap tma;
+    if (!make_tmap_f16_2d(&tma, a.p, rows, K, 128)) return -4;
+    const int fq = wtype == W_Q4_1 ? W_Q4_1 : W_Q4_0;
+    GemmArgs g1{&tma, a.as<__half>(), &w, res.as<__half>(), o1.as<__half>(), M, epilogue, fq};
+    GemmArgs g2 = g1; g2.out = o2.as<__half>();
+    if (!cuda_ok(launch_gemm_tc(g1, prop.multiProcessorCount, 0), "selftest gemm_tc launch")) return -6;
+    if (!cuda_ok(cudaDeviceSynchronize(), "selftest gemm_tc")) return -6;
+    if (!cuda_ok(launch_gemm_simt(g2, 0), "selftest gemm_simt launch")) return -7;
+    if (!cuda_ok(cudaDeviceSynchronize(), "selftest gemm_simt")) return -7;
+    return compare_h(o1.as<__half>(), o2.as<__half>(), (size_t) M * N, max_abs_err, max_ref) ? 0 : -8;
+}
+
+int32_t bertx_selftest_attention(int32_t n_sent, int32_t max_len, int32_t n_head, int32_t d_head, int32_t seed,
+                                 float * max_abs_err, float * max_ref) {
+    if (n_sent <= 0 || max_len <= 0 || (d_head != 32 && d_head != 64)) return -1;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { fprintf(stderr, "bertx_selftest_attention: no CUDA device\n"); return -2; }
+    std::mt19937 rng((uint32_t) seed);
+    std::normal_distribution<float> nd(0.f, 1.f);
+    const int H = n_head * d_head;
+    std::vector<int32_t> cu(n_sent + 1, 0);
+    for (int i = 0; i < n_sent; ++i) {
+        const int len = i == 0 ? max_len : 1 + (int) (rng() % (uint32_t) max_len);   // ragged, first is the longest
+        cu[i + 1] = cu[i] + len;
+    }
+    const size_t T = (size_t) cu[n_sent];
+    std::vector<uint16_t> hq(T * 3 * H);
+    for (auto & v : hq) v = f2h_bits(1.5f * nd(rng));
+    DevBuf qkv, dcu, o1, o2;
+    if (!qkv.alloc(hq.size() * 2) || !dcu.alloc(cu.size() * 4) || !o1.alloc(T * H * 2) || !o2.alloc(T * H * 2)) return -3;
+    cudaMemcpy(qkv.p, hq.data(), hq.size() * 2, cudaMemcpyHostToDevice);
+    cudaMemcpy(dcu.p, cu.data(), cu.size() * 4, cudaMemcpyHostToDevice);
+    cudaMemset(o1.p, 0xFF, T * H * 2);
+    if (!cuda_ok(launch_attention(qkv.as<__half>(), dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, 0), "selftest attention launch")) return -6;
+    if (!cuda_ok(cudaDeviceSynchronize(), "selftest attention")) return -6;
+    if (!cuda_ok(launch_attention_ref(qkv.as<__half>(), dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o2.as<__half>(), -1, 0), "selftest attention_ref launch")) return -7;
+    if (!cuda_ok(cudaDeviceSynchronize(), "selftest attention_ref")) return -7;
+    return compare_h(o1.as<__half>(), o2.as<__half>(), T * H, max_abs_err, max_ref) ? 0 : -8;
+}
+
+}  // extern "C"

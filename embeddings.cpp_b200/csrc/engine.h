@@ -103,3 +103,8 @@ struct Engine {
 bool cuda_ok(cudaError_t e, const char * what);
 
 }  // namespace b200
+
+// the opaque context of bert.h (reference bert.cpp:100-109)
+struct bert_ctx {
+    b200::Engine eng;
+};

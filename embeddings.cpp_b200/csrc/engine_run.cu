@@ -146,6 +146,10 @@ bool Engine::run_on_replica(Replica & r, const std::vector<int> & order, const s
 
 bool Engine::run_tokens(const int32_t * const * tokens, const int32_t * n_tokens, int n, float * const * out) {
     if (n <= 0) return true;
+    if (reps.empty()) {
+        fprintf(stderr, "libbert(b200): this context has no GPU replica (host-only load); there is no CPU path\n");
+        return false;
+    }
     for (int i = 0; i < n; ++i) {
         if (n_tokens[i] > hp.n_max_tokens) {                  // reference bert.cpp:867-871
             fprintf(stderr, "Too many tokens, maximum is %d\n", hp.n_max_tokens);

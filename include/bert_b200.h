@@ -14,6 +14,11 @@
 extern "C" {
 #endif
 
+/* Parse the model file and build the tokenizer only -- no GPU is touched.  bert_tokenize,
+ * bert_vocab_id_to_token, bert_n_embd, bert_n_max_tokens, bertx_tokenize_batch work on the
+ * returned context; every forward / encode call fails loudly (there is no CPU path). */
+BERT_API struct bert_ctx * bertx_load_host_only(const char * fname);
+
 /* Number of GPUs this context holds a weight replica on (BERT_CUDA_DEVICES / all visible). */
 BERT_API int32_t bertx_n_devices(struct bert_ctx * ctx);
 
