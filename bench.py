@@ -1,0 +1,282 @@
+"""bench.py -- embeddings/sec of the bert.h hot path on B200 (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload NAME]
+
+One process per GPU (torchrun for N > 1; RANK / LOCAL_RANK / WORLD_SIZE from the env).
+A "step" is one pass of the hot path over one batch of synthetic sentences; at the default
+workload (BASELINE.json configs[2], the configuration the metric is quoted on) that is
+bge-base-en-v1.5 q4_0, 512 sentences x 512 tokens PER GPU (weak scaling: sentences are
+sharded by rank, one weight replica per GPU, no data-path collective).
+
+Prints ONE JSON line on rank 0.  `value` = whole-job embeddings/s with token ids resident
+in HBM (CUDA events on the launch stream, max over ranks); `e2e` = the same through
+bert_encode_batch with host texts (tokenise + H2D + forward + D2H inside the timed region).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (shape, ftype, sentences per GPU per step, tokens per sentence)
+    "bge-base-q4_0-b512-s512": ("bge-base-en-v1.5", "q4_0", 512, 512),
+    "bge-small-f16-b256-s128": ("bge-small-en-v1.5", "f16", 256, 128),
+    "bge-large-q4_0-b1024-s256": ("bge-large-en-v1.5", "q4_0", 1024, 256),
+    "minilm-q4_0-b1738-var": ("all-MiniLM-L6-v2", "q4_0", 1738, 0),
+    "tiny-q4_0-b64-s64": ("tiny-d64", "q4_0", 64, 64),
+}
+DEFAULT_WORKLOAD = "bge-base-q4_0-b512-s512"
+
+
+def shard_range(n_items, rank, world):
+    """Contiguous shard [lo, hi) of n_items for `rank` of `world` (sizes differ by <= 1)."""
+    base, rem = divmod(n_items, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def flops_per_sentence(H, I, n_layer, n):
+    """Algorithmic FLOPs of one n-token sentence: GEMMs + attention."""
+    gemm = n_layer * 2 * n * (4 * H * H + 2 * H * I)
+    attn = n_layer * 4 * n * n * H
+    return gemm, attn
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"tflops_burst": d["bf16_tflops"], "tflops_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]),
+                "hbm_gbs": d["hbm_gbs"], "source": "measured"}
+    return {"tflops_burst": 1590.0, "tflops_sustained": 1400.0, "hbm_gbs": 6650.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """nvidia-smi SM clock / throttle-reason samples during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc, self.idx = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
+            self.thr = threading.Thread(target=self._read, daemon=True)
+            self.thr.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.thr.join(timeout=2)
+        sm = sorted(int(r[1]) for r in self.rows if len(r) >= 9 and r[1].isdigit())
+        mx = [int(r[2]) for r in self.rows if len(r) >= 9 and r[2].isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) < 9:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def make_inputs(shape, ftype, n_sent, n_tok, seed):
+    from oracle import fileformat  # the generator writes the reference's file format
+    from tools import synth
+    path = synth.model_path(shape, ftype)
+    mf_vocab = fileformat.read_model(path).vocab if False else None
+    # reading the whole model back just for the vocab is wasteful: regenerate it (deterministic)
+    vocab = synth.make_vocab(synth.SHAPES[shape][4], 0)
+    if n_tok > 0:
+        texts = synth.texts_exact_len(vocab, n_sent, n_tok, seed=seed)
+    else:
+        texts = synth.sample_client_texts(vocab, n_sent, seed=1738 + seed)
+    return path, texts
+
+
+def run_reference(args, shape, ftype, n_sent, n_tok, rank, world):
+    """--impl reference: the reference's own ggml CPU path (oracle/_ref) on a bounded sample."""
+    if rank != 0:
+        return
+    from oracle import reflib
+    path, texts = make_inputs(shape, ftype, n_sent, n_tok, seed=0)
+    sample = 2 if n_tok >= 256 else (8 if n_tok > 0 else 32)
+    texts = texts[:sample]
+    ref = reflib.RefBert(path)
+    toks = [ref.tokenize(t) for t in texts]
+    for _ in range(args.warmup):
+        ref.forward_tokens(toks[:1], chunk=1)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        ref.forward_tokens(toks, chunk=min(sample, 8))
+    dt = time.perf_counter() - t0
+    v = sample * args.steps / dt
+    cores = os.cpu_count() or 1
+    base = {"value": v, "unit": "embeddings/s", "cores": cores, "kind": "reference",
+            "sample": f"{sample} sentences x {n_tok or 'var'} tokens per step, bert_forward_batch, n_threads={cores}"}
+    print(json.dumps({"metric": "embeddings/s", "value": v, "unit": "embeddings/s", "impl": "reference",
+                      "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+                      "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+                      "vs_baseline": None, "dtype": "q4_0 x q8_0 int8 dot, f32 accumulate (ggml CPU)" if "q4" in ftype else ftype,
+                      "data": "synthetic", "config": {"workload": args.workload, "model_shape": shape, "weights": ftype,
+                                                       "seq_len": n_tok, "sample_sentences_per_step": sample},
+                      "cpu_baseline": base,
+                      "e2e": {"value": v, "unit": "embeddings/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=list(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    shape, ftype, n_sent, n_tok = WORKLOADS[args.workload]
+
+    if args.impl == "reference":
+        run_reference(args, shape, ftype, n_sent, n_tok, rank, world)
+        return
+
+    os.environ["BERT_CUDA_DEVICES"] = str(local_rank)          # one replica per process
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import __graft_entry__ as ge
+    pkg = ge.load_package()
+    if world > 1:
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # rank 0 generates the (cached) model file first so ranks do not race on it
+    if rank == 0:
+        path, texts = make_inputs(shape, ftype, n_sent, n_tok, seed=0)
+    barrier()
+    path, texts = make_inputs(shape, ftype, n_sent, n_tok, seed=rank)
+    devnull = os.open(os.devnull, os.O_WRONLY)
+    saved = os.dup(1)
+    os.dup2(devnull, 1)                                         # keep the load banner off stdout
+    try:
+        m = pkg.BertModel(path)
+    finally:
+        os.dup2(saved, 1)
+    hp = m.hparams()
+    H, I, NL = hp["n_embd"], hp["n_intermediate"], hp["n_layer"]
+    ids, lens = m.tokenize_batch(texts)
+    T = int(lens.sum())
+    m.stage(ids, lens)
+
+    # ---- device-resident throughput (`value`)
+    m.run_staged(reps=args.warmup)
+    sampler = ClockSampler(local_rank)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    l0 = m.kernel_launches()
+    ms, _ = m.run_staged(reps=args.steps)
+    launches = m.kernel_launches() - l0
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms = max_over_ranks(ms)
+    value = world * n_sent * args.steps / (ms / 1e3)
+
+    # ---- end to end through bert_encode_batch (host texts in, host floats out)
+    for _ in range(2):
+        m.encode(texts)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        out = m.encode(texts)
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    barrier()
+    e2e_value = world * n_sent * args.steps / e2e_s
+
+    # ---- roofline of the dominant kernel (the tcgen05 GEMM), timed live with events
+    prof = m.profile_staged()
+    peaks = measured_peaks()
+    gemm_ms, gemm_launches = prof["gemm"]
+    gemm_flops = sum(flops_per_sentence(H, I, NL, int(n))[0] for n in lens)
+    attn_flops = sum(flops_per_sentence(H, I, NL, int(n))[1] for n in lens)
+    achieved = gemm_flops / (gemm_ms / 1e3) / 1e12 if gemm_ms > 0 else 0.0
+    total_prof_ms = sum(v[0] for v in prof.values())
+    roofline = {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05, q4 dequant fused)" if "q4" in ftype else "gemm_tc_kernel (tcgen05)",
+                "achieved": achieved, "peak": peaks["tflops_sustained"], "unit": "TFLOP/s",
+                "frac": achieved / peaks["tflops_sustained"], "traffic": None,
+                "peak_source": peaks["source"] + " sustained bf16 (kernel timed inside a long step)",
+                "launches_per_step": gemm_launches, "avg_launch_ms": gemm_ms / max(gemm_launches, 1),
+                "algorithmic_flops_per_step": gemm_flops,
+                "share_of_step": gemm_ms / total_prof_ms if total_prof_ms else None,
+                "by_kernel_ms": {k: round(v[0], 3) for k, v in prof.items()},
+                "whole_forward_tflops": (gemm_flops + attn_flops) * world / (ms / args.steps / 1e3) / 1e12 / world}
+
+    line = {"metric": "embeddings/s", "value": value, "unit": "embeddings/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f16 x f16 -> f32 (tcgen05 kind::f16; q4 weights dequantised in the mainloop)",
+            "data": "synthetic",
+            "config": {"workload": args.workload, "model_shape": shape, "weights": ftype, "sentences_per_gpu": n_sent,
+                       "seq_len": n_tok, "tokens_per_gpu_per_step": T, "parallelism": f"dp{world} (sentence shards, no collective)",
+                       "l2": "inputs larger than L2: activations of one step are %.0f MB per buffer" % (T * H * 2 / 1e6)},
+            "e2e": {"value": e2e_value, "unit": "embeddings/s", "h2d_bytes_per_step": int(T * 4 + (n_sent + 1) * 4),
+                    "d2h_bytes_per_step": int(n_sent * H * 4)},
+            "gpu_launches": int(launches), "roofline": roofline, "clocks": clocks}
+
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        from oracle import reflib                               # bench cpu_baseline leg (checker timed, not shipped)
+        if reflib.available():
+            sample = 4 if n_tok >= 256 else 16
+            ref = reflib.RefBert(path)
+            toks = [ref.tokenize(t) for t in texts[:sample]]
+            ref.forward_tokens(toks[:1], chunk=1)
+            t0 = time.perf_counter()
+            want = ref.forward_tokens(toks, chunk=min(sample, 8))
+            dt = time.perf_counter() - t0
+            cos = (out[:sample] * want).sum(1) / np.linalg.norm(out[:sample], axis=1) / np.linalg.norm(want, axis=1)
+            line["cpu_baseline"] = {"value": sample / dt, "unit": "embeddings/s", "cores": os.cpu_count(), "kind": "reference",
+                                    "sample": f"{sample} sentences x {n_tok or 'var'} tokens, bert_forward_batch of oracle/_ref/libbert_ref.so",
+                                    "parity_min_cosine": float(cos.min()), "parity_max_abs": float(np.abs(out[:sample] - want).max())}
+        else:
+            line["cpu_baseline"] = {"value": None, "unit": "embeddings/s", "cores": os.cpu_count(), "kind": "reference",
+                                    "sample": "oracle/_ref not built on this box"}
+    if rank == 0:
+        print(json.dumps(line))
+    m.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
