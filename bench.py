@@ -98,11 +98,9 @@ class ClockSampler:
 
 
 def make_inputs(shape, ftype, n_sent, n_tok, seed):
-    from oracle import fileformat  # the generator writes the reference's file format
     from tools import synth
     path = synth.model_path(shape, ftype)
-    mf_vocab = fileformat.read_model(path).vocab if False else None
-    # reading the whole model back just for the vocab is wasteful: regenerate it (deterministic)
+    # the vocabulary is regenerated (deterministic) instead of reading the model back
     vocab = synth.make_vocab(synth.SHAPES[shape][4], 0)
     if n_tok > 0:
         texts = synth.texts_exact_len(vocab, n_sent, n_tok, seed=seed)
