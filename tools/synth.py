@@ -66,8 +66,14 @@ def make_vocab(n_vocab, seed=0):
 
 
 def make_weights(H, I, n_layer, n_vocab, n_max_tokens=512, seed=0):
-    """Random weights with BERT-like statistics (dense sigma chosen so activations neither
-    vanish nor blow up through the stack; LayerNorm gamma near 1)."""
+    """Random weights with BERT-like statistics: unit-variance attention logits (Q/K sigma
+    1/sqrt(H)) and sub-layer outputs at about half the residual stream's scale (O and FFN-out
+    sigma 0.5/sqrt(fan_in)), LayerNorm gamma near 1.  Sharper/larger choices make a 12-layer
+    random-weight stack chaotic: the reference's own q8 activation rounding then flips enough
+    decisions that the reference disagrees WITH ITSELF across batch compositions
+    (bert_forward_batch of 4 vs of 1: cosine 0.99988 on the bge-base shape, measured), which
+    would make a 0.9999 parity bar meaningless.  With these statistics the reference is
+    self-consistent to 0.999999 and parity is a real test."""
     rng = np.random.default_rng(seed)
 
     def mat(o, i, s):
@@ -86,19 +92,19 @@ def make_weights(H, I, n_layer, n_vocab, n_max_tokens=512, seed=0):
     sa = 1.0 / np.sqrt(H)
     for i in range(n_layer):
         p = f"encoder.layer.{i}."
-        t[p + "attention.self.query.weight"] = mat(H, H, 2.0 * sa)
+        t[p + "attention.self.query.weight"] = mat(H, H, 1.0 * sa)
         t[p + "attention.self.query.bias"] = vec(H, 0.1)
-        t[p + "attention.self.key.weight"] = mat(H, H, 2.0 * sa)
+        t[p + "attention.self.key.weight"] = mat(H, H, 1.0 * sa)
         t[p + "attention.self.key.bias"] = vec(H, 0.1)
         t[p + "attention.self.value.weight"] = mat(H, H, 1.0 * sa)
         t[p + "attention.self.value.bias"] = vec(H, 0.05)
-        t[p + "attention.output.dense.weight"] = mat(H, H, 1.0 * sa)
+        t[p + "attention.output.dense.weight"] = mat(H, H, 0.5 * sa)
         t[p + "attention.output.dense.bias"] = vec(H, 0.05)
         t[p + "attention.output.LayerNorm.weight"] = vec(H, 0.1, 1.0)
         t[p + "attention.output.LayerNorm.bias"] = vec(H, 0.05)
         t[p + "intermediate.dense.weight"] = mat(I, H, 1.0 * sa)
         t[p + "intermediate.dense.bias"] = vec(I, 0.1)
-        t[p + "output.dense.weight"] = mat(H, I, 1.0 / np.sqrt(I))
+        t[p + "output.dense.weight"] = mat(H, I, 0.5 / np.sqrt(I))
         t[p + "output.dense.bias"] = vec(H, 0.05)
         t[p + "output.LayerNorm.weight"] = vec(H, 0.1, 1.0)
         t[p + "output.LayerNorm.bias"] = vec(H, 0.05)
@@ -112,7 +118,7 @@ def model_path(shape, ftype, seed=0, n_layer=None, n_max_tokens=512):
         nl = n_layer
     ft = fileformat.FTYPE_IDS[ftype] if isinstance(ftype, str) else ftype
     os.makedirs(CACHE, exist_ok=True)
-    tag = f"{shape}-L{nl}-P{n_max_tokens}-s{seed}-{fileformat.FTYPE_NAMES[ft]}"
+    tag = f"{shape}-L{nl}-P{n_max_tokens}-s{seed}-v2-{fileformat.FTYPE_NAMES[ft]}"
     path = os.path.join(CACHE, f"ggml-model-{tag}.bin")
     if os.path.exists(path):
         return path
