@@ -72,6 +72,8 @@ def lib():
     L.bertx_profile_staged.argtypes = [vp, c_i32, pf, ctypes.POINTER(c_i64)]
     L.bertx_selftest_gemm.restype = c_i32
     L.bertx_selftest_gemm.argtypes = [c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, pf, pf]
+    L.bertx_bench_gemm.restype = c_i32
+    L.bertx_bench_gemm.argtypes = [c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, pf]
     L.bertx_selftest_attention.restype = c_i32
     L.bertx_selftest_attention.argtypes = [c_i32, c_i32, c_i32, c_i32, c_i32, pf, pf]
     _lib = L
@@ -204,3 +206,13 @@ def selftest_attention(n_sent, max_len, n_head, d_head, seed=0):
     err, ref = ctypes.c_float(0), ctypes.c_float(0)
     rc = lib().bertx_selftest_attention(n_sent, max_len, n_head, d_head, seed, ctypes.byref(err), ctypes.byref(ref))
     return rc, err.value, ref.value
+
+
+def bench_gemm(M, N, K, wtype, epilogue, reps=20):
+    """(ms per launch, TFLOP/s) of the tcgen05 GEMM kernel on random data."""
+    ms = ctypes.c_float(0)
+    rc = lib().bertx_bench_gemm(M, N, K, wtype, epilogue, reps, ctypes.byref(ms))
+    if rc != 0:
+        raise RuntimeError(f"bertx_bench_gemm failed ({rc})")
+    per = ms.value / reps
+    return per, 2.0 * M * N * K / (per * 1e-3) / 1e12

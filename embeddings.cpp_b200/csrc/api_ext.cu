@@ -144,8 +144,12 @@ bool compare_h(const __half * da, const __half * db, size_t n, float * max_err, 
 
 extern "C" {
 
-int32_t bertx_selftest_gemm(int32_t M, int32_t N, int32_t K, int32_t wtype, int32_t epilogue, int32_t seed,
-                            float * max_abs_err, float * max_ref) {
+}  // extern "C"
+
+// reps == 0: run the tcgen05 kernel and the SIMT kernel once and compare;
+// reps  > 0: time `reps` back-to-back launches of the tcgen05 kernel (CUDA events, after one warm-up)
+static int32_t gemm_test_impl(int32_t M, int32_t N, int32_t K, int32_t wtype, int32_t epilogue, int32_t seed,
+                              float * max_abs_err, float * max_ref, int reps, float * ms_out) {
     if (M <= 0 || N % 64 || K % 64 || wtype < 1 || wtype > 3) return -1;
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { fprintf(stderr, "bertx_selftest_gemm: no CUDA device\n"); return -2; }
@@ -201,9 +205,35 @@ int32_t bertx_selftest_gemm(int32_t M, int32_t N, int32_t K, int32_t wtype, int3
     GemmArgs g2 = g1; g2.out = o2.as<__half>();
     if (!cuda_ok(launch_gemm_tc(g1, prop.multiProcessorCount, 0), "selftest gemm_tc launch")) return -6;
     if (!cuda_ok(cudaDeviceSynchronize(), "selftest gemm_tc")) return -6;
+    if (reps > 0) {
+        cudaEvent_t e0, e1;
+        cudaEventCreate(&e0); cudaEventCreate(&e1);
+        cudaEventRecord(e0, 0);
+        for (int i = 0; i < reps; ++i) launch_gemm_tc(g1, prop.multiProcessorCount, 0);
+        cudaEventRecord(e1, 0);
+        const bool ok = cuda_ok(cudaDeviceSynchronize(), "bench gemm_tc");
+        float ms = 0.f;
+        if (ok) cudaEventElapsedTime(&ms, e0, e1);
+        cudaEventDestroy(e0); cudaEventDestroy(e1);
+        *ms_out = ms;
+        return ok ? 0 : -6;
+    }
     if (!cuda_ok(launch_gemm_simt(g2, 0), "selftest gemm_simt launch")) return -7;
     if (!cuda_ok(cudaDeviceSynchronize(), "selftest gemm_simt")) return -7;
     return compare_h(o1.as<__half>(), o2.as<__half>(), (size_t) M * N, max_abs_err, max_ref) ? 0 : -8;
+}
+
+extern "C" {
+
+int32_t bertx_selftest_gemm(int32_t M, int32_t N, int32_t K, int32_t wtype, int32_t epilogue, int32_t seed,
+                            float * max_abs_err, float * max_ref) {
+    return gemm_test_impl(M, N, K, wtype, epilogue, seed, max_abs_err, max_ref, 0, nullptr);
+}
+
+int32_t bertx_bench_gemm(int32_t M, int32_t N, int32_t K, int32_t wtype, int32_t epilogue, int32_t reps, float * ms_total) {
+    float a = 0.f, b = 0.f;
+    if (reps <= 0) return -1;
+    return gemm_test_impl(M, N, K, wtype, epilogue, 1, &a, &b, reps, ms_total);
 }
 
 int32_t bertx_selftest_attention(int32_t n_sent, int32_t max_len, int32_t n_head, int32_t d_head, int32_t seed,

@@ -61,6 +61,9 @@ BERT_API int64_t bertx_kernel_launches(struct bert_ctx * ctx);
  * bit2 residual, bit3 q8 fake-quant of the output.  Return 0 on success (ran), <0 error. */
 BERT_API int32_t bertx_selftest_gemm(int32_t M, int32_t N, int32_t K, int32_t wtype, int32_t epilogue,
                                      int32_t seed, float * max_abs_err, float * max_ref);
+/* Time `reps` back-to-back launches of the tcgen05 GEMM on random data (CUDA events). */
+BERT_API int32_t bertx_bench_gemm(int32_t M, int32_t N, int32_t K, int32_t wtype, int32_t epilogue, int32_t reps,
+                                  float * ms_total);
 BERT_API int32_t bertx_selftest_attention(int32_t n_sent, int32_t max_len, int32_t n_head, int32_t d_head,
                                           int32_t seed, float * max_abs_err, float * max_ref);
 
