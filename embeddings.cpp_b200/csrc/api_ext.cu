@@ -198,10 +198,11 @@ static int32_t gemm_test_impl(int32_t M, int32_t N, int32_t K, int32_t wtype, in
         w.qnib = nib.as<uint4>(); w.qd = qd.as<__half>(); w.qm = wtype == W_Q4_1 ? qm.as<__half>() : nullptr;
         memset(&w.tmap, 0, sizeof(w.tmap));
     }
-    CUtensorMap tma;
+    CUtensorMap tma, tmo;
     if (!make_tmap_f16_2d(&tma, a.p, rows, K, 128)) return -4;
+    if (!make_tmap_f16_2d(&tmo, o1.p, M, N, 32)) return -4;        // exactly M rows: the store must clip the tail tile
     const int fq = wtype == W_Q4_1 ? W_Q4_1 : W_Q4_0;
-    GemmArgs g1{&tma, a.as<__half>(), &w, res.as<__half>(), o1.as<__half>(), M, epilogue, fq};
+    GemmArgs g1{&tma, &tmo, a.as<__half>(), &w, res.as<__half>(), o1.as<__half>(), M, epilogue, fq};
     GemmArgs g2 = g1; g2.out = o2.as<__half>();
     if (!cuda_ok(launch_gemm_tc(g1, prop.multiProcessorCount, 0), "selftest gemm_tc launch")) return -6;
     if (!cuda_ok(cudaDeviceSynchronize(), "selftest gemm_tc")) return -6;

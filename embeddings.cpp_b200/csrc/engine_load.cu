@@ -330,7 +330,9 @@ bool Engine::alloc_workspace(Replica & r) {
     cudaMemsetAsync(r.x1, 0, rows * H * 2, r.stream);
     cudaMemsetAsync(r.mid, 0, rows * I * 2, r.stream);
     if (!make_tmap_f16_2d(&r.tm_xin, r.xq, rows, H, 128) || !make_tmap_f16_2d(&r.tm_ctx, r.ctx, rows, H, 128) ||
-        !make_tmap_f16_2d(&r.tm_x1in, r.x1q, rows, H, 128) || !make_tmap_f16_2d(&r.tm_mid, r.mid, rows, I, 128)) {
+        !make_tmap_f16_2d(&r.tm_x1in, r.x1q, rows, H, 128) || !make_tmap_f16_2d(&r.tm_mid, r.mid, rows, I, 128) ||
+        !make_tmap_f16_2d(&r.to_qkv, r.qkv, rows, 3 * H, 32) || !make_tmap_f16_2d(&r.to_y, r.y, rows, H, 32) ||
+        !make_tmap_f16_2d(&r.to_mid, r.mid, rows, I, 32)) {
         fprintf(stderr, "bert_load_from_file: cuTensorMapEncodeTiled failed for an activation map\n");
         return false;
     }

@@ -29,7 +29,8 @@ template <int BN> struct GemmCfg {
     static constexpr int kStageBytes = kABytes + kBBytes;
     static constexpr int kTmemCols = (2 * BN <= 128) ? 128 : (2 * BN <= 256 ? 256 : 512);
     static constexpr int kAccStride = BN <= 64 ? 64 : (BN <= 128 ? 128 : 256);
-    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+    static constexpr int kOutBytes = 4 * 2 * 4096;      // 4 epilogue warps x 2 buffers x [32 rows][128 B]
+    static constexpr int kSmemBytes = kStages * kStageBytes + kOutBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
 struct GemmParams {
@@ -38,12 +39,55 @@ struct GemmParams {
     int M, N, K, epilogue, fq_type;
 };
 
-__device__ __forceinline__ float gelu_ref_numerics(float x) {
-    // reference: y = f16(gelu_f32(f16(x))) through a 64K-entry table (ggml.c:3561-3580, 4332)
-    const float f = __half2float(__float2half_rn(x));
-    const float u = 0.79788456080286535587989211986876f * f * (1.0f + 0.044715f * f * f);
-    const float t = 1.0f - 2.0f / (__expf(2.0f * u) + 1.0f);          // tanh(u)
-    return __half2float(__float2half_rn(0.5f * f * (1.0f + t)));
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+    float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y;
+}
+// round two floats to fp16 and back (what passing a value through an f16 table index does)
+__device__ __forceinline__ float2 round_h2(float2 v) {
+    return __half22float2(__floats2half2_rn(v.x, v.y));
+}
+// Reference GELU numerics: y = f16(gelu_f32(f16(x))) through a 64K-entry table
+// (ggml.c:3561-3580, 4332).  tanh-GELU rewritten as f / (1 + exp(-2u)), u = sqrt(2/pi) f (1 + 0.044715 f^2),
+// with ex2.approx / rcp.approx (2 MUFU per element) and packed f32x2 arithmetic.
+__device__ __forceinline__ float2 gelu2_ref_numerics(float2 v) {
+    const float c1 = -2.0f * 1.4426950408889634f * 0.79788456080286535588f;
+    const float c2 = c1 * 0.044715f;
+    const float2 f = round_h2(v);
+    const float2 p = __ffma2_rn(__fmul2_rn(f, f), make_float2(c2, c2), make_float2(c1, c1));
+    const float2 z = __fmul2_rn(f, p);
+    const float2 d = __fadd2_rn(make_float2(ex2_approx(z.x), ex2_approx(z.y)), make_float2(1.f, 1.f));
+    return round_h2(__fmul2_rn(f, make_float2(rcp_approx(d.x), rcp_approx(d.y))));
+}
+// q8 fake-quant of 32 consecutive values (16 float2) held by one thread; rint via the
+// 1.5*2^23 magic constant (round-half-even, |x| <= 127 here) to stay on the FMA pipe
+__device__ __forceinline__ void fake_quant32_v2(float2 (&v)[16], int fq_type) {
+    float amax = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) amax = fmaxf(amax, fmaxf(fabsf(v[i].x), fabsf(v[i].y)));
+    const float d = amax / 127.f;
+    const float id = amax != 0.f ? 127.f / amax : 0.f;
+    const float dd = fq_type == W_Q4_0 ? __half2float(__float2half_rn(d)) : d;
+    const float2 id2 = make_float2(id, id), dd2 = make_float2(dd, dd);
+    const float2 mg = make_float2(12582912.f, 12582912.f), nmg = make_float2(-12582912.f, -12582912.f);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const float2 r = __fadd2_rn(__ffma2_rn(v[i], id2, mg), nmg);
+        v[i] = __fmul2_rn(r, dd2);
+    }
+}
+__device__ __forceinline__ void tma_store_2d(const void * tmap, const void * smem_src, int32_t c0, int32_t c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 :: "l"(tmap), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void tma_store_wait_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" :: "n"(N) : "memory");
+}
+template <int N> __device__ __forceinline__ void tma_store_wait_all() {
+    asm volatile("cp.async.bulk.wait_group %0;" :: "n"(N) : "memory");
 }
 
 // two nibbles -> two fp16 weights.  `w` holds e(2i) at bits [4i,4i+4), e(2i+1) at [16+4i,..)
@@ -62,14 +106,15 @@ __device__ __forceinline__ uint32_t dq_pair(uint32_t w, int i, __half2 d2, __hal
 template <int BN, int WT>
 __global__ void __launch_bounds__(WT == W_F16 ? 192 : 320, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-               const GemmParams p) {
+               const __grid_constant__ CUtensorMap tmap_out, const GemmParams p) {
     using Cfg = GemmCfg<BN>;
     constexpr int S = Cfg::kStages;
     extern __shared__ uint8_t smem_raw[];
     uint8_t * smem = (uint8_t *) (((uintptr_t) smem_raw + 1023) & ~(uintptr_t) 1023);
     uint8_t * smem_a = smem;                                  // S x 16 KB
     uint8_t * smem_b = smem + S * Cfg::kABytes;               // S x BN*128 B
-    uint64_t * bars = (uint64_t *) (smem + S * Cfg::kStageBytes);
+    uint8_t * smem_out = smem + S * Cfg::kStageBytes;         // 4 warps x 2 x 4 KB staging for TMA stores
+    uint64_t * bars = (uint64_t *) (smem + S * Cfg::kStageBytes + Cfg::kOutBytes);
     uint64_t * full = bars;                 // [S]
     uint64_t * empty = bars + S;            // [S]
     uint64_t * tfull = bars + 2 * S;        // [2]
@@ -85,6 +130,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmap_a);
         if (WT == W_F16) tma_prefetch_desc(&tmap_b);
+        tma_prefetch_desc(&tmap_out);
         for (int s = 0; s < S; ++s) {
             mbar_init(&full[s], WT == W_F16 ? 1 : 1 + 4);
             mbar_init(&empty[s], 1);
@@ -143,67 +189,97 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         }
     } else if (warp < 6) {
         // ------------------------------------------------------------ epilogue (4 warps)
+        // Per 64-column box: (residual: coalesced LDG -> swizzled smem) ; TMEM -> registers ;
+        // bias / GELU / + residual (own row from smem) / q8 fake-quant ; fp16 -> swizzled smem ;
+        // one TMA store of the warp's [32 rows x 64 cols] sub-box.  Global traffic is whole
+        // 128-B rows in both directions; everything is warp-local (no CTA barrier).
         const int q = warp & 3;                    // TMEM lane quadrant this warp may access
+        uint8_t * stage_base = smem_out + (warp - 2) * 2 * 4096;
         int it = 0;
+        uint32_t box_ctr = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
             const int m0 = (tile / num_n) * BM, n0 = (tile % num_n) * BN;
             const int acc = it & 1;
             const uint32_t acc_ph = (it >> 1) & 1;
+            const int wrow0 = m0 + q * 32;                  // first row of this warp's sub-tile
             mbar_wait(&tfull[acc], acc_ph);
             tc_fence_after_sync();
-            const int row = m0 + q * 32 + lane;
-            const bool row_ok = row < p.M;
-            const size_t row_off = (size_t) row * p.N;
 #pragma unroll 1
-            for (int j = 0; j < BN / 32; ++j) {
-                uint32_t r[32];
-                tmem_ld_32x32b_x32(tmem_base + ((uint32_t) (q * 32) << 16) + acc * Cfg::kAccStride + j * 32, r);
-                tmem_ld_wait();
-                const int c0 = n0 + j * 32;
-                float v[32];
+            for (int b = 0; b < BN / 64; ++b, ++box_ctr) {
+                uint8_t * st = stage_base + (box_ctr & 1) * 4096;
+                const int c0 = n0 + b * 64;
+                // the TMA store that last read this buffer (two boxes ago) must be done reading
+                if (lane == 0) tma_store_wait_read<1>();
+                __syncwarp();
+                if (p.epilogue & EPI_RESIDUAL) {
+                    uint4 rr[8];
 #pragma unroll
-                for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-                if (p.epilogue & EPI_BIAS) {
-#pragma unroll
-                    for (int i = 0; i < 32; i += 4) {
-                        const float4 b = __ldg(reinterpret_cast<const float4 *>(p.bias + c0 + i));
-                        v[i] += b.x; v[i + 1] += b.y; v[i + 2] += b.z; v[i + 3] += b.w;
+                    for (int i = 0; i < 8; ++i) {
+                        const int id = lane + 32 * i, r = id >> 3, c = id & 7;
+                        rr[i] = (wrow0 + r < p.M)
+                            ? __ldg(reinterpret_cast<const uint4 *>(p.residual + (size_t) (wrow0 + r) * p.N + c0) + c)
+                            : make_uint4(0, 0, 0, 0);
                     }
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int id = lane + 32 * i, r = id >> 3, c = id & 7;
+                        *reinterpret_cast<uint4 *>(st + r * 128 + ((c ^ (r & 7)) << 4)) = rr[i];
+                    }
+                    __syncwarp();
                 }
-                if (p.epilogue & EPI_GELU) {
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) v[i] = gelu_ref_numerics(v[i]);
-                }
-                if ((p.epilogue & EPI_RESIDUAL) && row_ok) {
-                    const uint4 * rp = reinterpret_cast<const uint4 *>(p.residual + row_off + c0);
+                for (int hh = 0; hh < 2; ++hh) {
+                    uint32_t r[32];
+                    tmem_ld_32x32b_x32(tmem_base + ((uint32_t) (q * 32) << 16) + acc * Cfg::kAccStride + b * 64 + hh * 32, r);
+                    tmem_ld_wait();
+                    float2 v[16];
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const uint4 u = __ldg(rp + i);
-                        const __half2 * h = reinterpret_cast<const __half2 *>(&u);
+                    for (int i = 0; i < 16; ++i) v[i] = make_float2(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1]));
+                    if (p.epilogue & EPI_BIAS) {
 #pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            const float2 f = __half22float2(h[e]);
-                            v[i * 8 + 2 * e] += f.x; v[i * 8 + 2 * e + 1] += f.y;
+                        for (int i = 0; i < 8; ++i) {
+                            const float4 bb = __ldg(reinterpret_cast<const float4 *>(p.bias + c0 + hh * 32) + i);
+                            v[2 * i] = __fadd2_rn(v[2 * i], make_float2(bb.x, bb.y));
+                            v[2 * i + 1] = __fadd2_rn(v[2 * i + 1], make_float2(bb.z, bb.w));
                         }
                     }
-                }
-                if (p.epilogue & EPI_FAKEQUANT) fake_quant32(v, p.fq_type);
-                if (row_ok) {
-                    uint4 * op = reinterpret_cast<uint4 *>(p.out + row_off + c0);
+                    if (p.epilogue & EPI_GELU) {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) v[i] = gelu2_ref_numerics(v[i]);
+                    }
+                    if (p.epilogue & EPI_RESIDUAL) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const int c = hh * 4 + i;
+                            const uint4 u = *reinterpret_cast<const uint4 *>(st + lane * 128 + ((c ^ (lane & 7)) << 4));
+                            const __half2 * h = reinterpret_cast<const __half2 *>(&u);
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) v[i * 4 + e] = __fadd2_rn(v[i * 4 + e], __half22float2(h[e]));
+                        }
+                    }
+                    if (p.epilogue & EPI_FAKEQUANT) fake_quant32_v2(v, p.fq_type);
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
+                        const int c = hh * 4 + i;
                         uint4 u;
                         __half2 * h = reinterpret_cast<__half2 *>(&u);
 #pragma unroll
-                        for (int e = 0; e < 4; ++e) h[e] = __floats2half2_rn(v[i * 8 + 2 * e], v[i * 8 + 2 * e + 1]);
-                        op[i] = u;
+                        for (int e = 0; e < 4; ++e) h[e] = __floats2half2_rn(v[i * 4 + e].x, v[i * 4 + e].y);
+                        *reinterpret_cast<uint4 *>(st + lane * 128 + ((c ^ (lane & 7)) << 4)) = u;
                     }
+                }
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                    tma_store_2d(&tmap_out, st, c0, wrow0);
+                    tma_store_commit();
                 }
             }
             tc_fence_before_sync();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tempty[acc]);
         }
+        if (lane == 0) tma_store_wait_all<0>();
     } else {
         // ------------------------------------------------------------ q4 dequant producers (4 warps)
         if (WT != W_F16) {
@@ -269,7 +345,7 @@ static cudaError_t launch_one(const GemmArgs & g, int num_sms, cudaStream_t st) 
     const int tiles = ((g.M + BM - 1) / BM) * (w.N / BN);
     const int grid = tiles < num_sms ? tiles : num_sms;
     if (grid <= 0) return cudaSuccess;
-    kern<<<grid, WT == W_F16 ? 192 : 320, Cfg::kSmemBytes, st>>>(*g.tmap_a, w.tmap, p);
+    kern<<<grid, WT == W_F16 ? 192 : 320, Cfg::kSmemBytes, st>>>(*g.tmap_a, w.tmap, *g.tmap_out, p);
     return cudaGetLastError();
 }
 

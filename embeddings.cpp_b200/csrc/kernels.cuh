@@ -37,6 +37,7 @@ struct DevWeight {
 
 struct GemmArgs {
     const CUtensorMap * tmap_a;     // host pointer to the A map (copied into kernel params)
+    const CUtensorMap * tmap_out;   // output map, box {64 cols, 32 rows} (epilogue TMA stores)
     const __half * a;               // A [M][K] fp16 (used by the SIMT validation kernel only)
     const DevWeight * w;
     const __half * residual;        // [M][N] fp16 or null

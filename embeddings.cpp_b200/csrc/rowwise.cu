@@ -143,17 +143,88 @@ embed_ln_kernel(const DevTable word, const float * __restrict__ postype,
               out_fq ? out_fq + (size_t) row * H : nullptr, fq_type);
 }
 
+// K3.  Lane l owns the 16-B chunks c = l + 32 i (8 fp16 each) of the row, so every warp-level
+// load/store is one fully coalesced 512-B access; a q8 block (32 values) is 4 adjacent lanes.
+template <int NCH>
 __global__ void __launch_bounds__(ROWS_PER_CTA * 32)
 ln_kernel(const __half * __restrict__ x, const float * __restrict__ gamma, const float * __restrict__ beta,
           int T, int H, __half * __restrict__ out, __half * __restrict__ out_fq, int fq_type) {
     const int row = blockIdx.x * ROWS_PER_CTA + (threadIdx.x >> 5);
     if (row >= T) return;
     const int lane = threadIdx.x & 31;
-    const bool active = lane < H / 32;
-    float v[32];
-    if (active) load32_h(x + (size_t) row * H + lane * 32, v);
-    ln_finish(v, active, H, lane, gamma, beta, out + (size_t) row * H,
-              out_fq ? out_fq + (size_t) row * H : nullptr, fq_type);
+    const int nchunk = H / 8;
+    float v[NCH][8];
+    const uint4 * xr = reinterpret_cast<const uint4 *>(x + (size_t) row * H);
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+        const int c = lane + 32 * i;
+        if (c < nchunk) {
+            const uint4 u = __ldg(xr + c);
+            const __half2 * h = reinterpret_cast<const __half2 *>(&u);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float2 f = __half22float2(h[e]);
+                v[i][2 * e] = f.x; v[i][2 * e + 1] = f.y;
+                s += f.x + f.y;
+            }
+        } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[i][e] = 0.f;
+        }
+    }
+    const float mean = warp_sum(s) / (float) H;
+    float s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+        if (lane + 32 * i < nchunk) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) { v[i][e] -= mean; s2 += v[i][e] * v[i][e]; }
+        }
+    }
+    const float var = warp_sum(s2) / (float) H;
+    const float scale = 1.0f / sqrtf(var + 1e-5f);
+    uint4 * orow = reinterpret_cast<uint4 *>(out + (size_t) row * H);
+    uint4 * qrow = out_fq ? reinterpret_cast<uint4 *>(out_fq + (size_t) row * H) : nullptr;
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+        const int c = lane + 32 * i;
+        const bool ok = c < nchunk;
+        if (ok) {
+            const float4 g0 = __ldg(reinterpret_cast<const float4 *>(gamma) + 2 * c);
+            const float4 g1 = __ldg(reinterpret_cast<const float4 *>(gamma) + 2 * c + 1);
+            const float4 b0 = __ldg(reinterpret_cast<const float4 *>(beta) + 2 * c);
+            const float4 b1 = __ldg(reinterpret_cast<const float4 *>(beta) + 2 * c + 1);
+            const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+            const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+            uint4 u;
+            __half2 * h = reinterpret_cast<__half2 *>(&u);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[i][e] = v[i][e] * scale * g[e] + b[e];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) h[e] = __floats2half2_rn(v[i][2 * e], v[i][2 * e + 1]);
+            orow[c] = u;
+        }
+        if (qrow) {                                        // warp-uniform branch: all lanes shuffle
+            float amax = 0.f;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) amax = fmaxf(amax, fabsf(v[i][e]));
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+            const float d = amax / 127.f;
+            const float id = amax != 0.f ? 127.f / amax : 0.f;
+            const float dd = fq_type == W_Q4_0 ? __half2float(__float2half_rn(d)) : d;
+            if (ok) {
+                uint4 u;
+                __half2 * h = reinterpret_cast<__half2 *>(&u);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    h[e] = __floats2half2_rn(rintf(v[i][2 * e] * id) * dd, rintf(v[i][2 * e + 1] * id) * dd);
+                }
+                qrow[c] = u;
+            }
+        }
+    }
 }
 
 // one CTA per sentence; thread = (8-column chunk, token stripe)
@@ -215,8 +286,12 @@ cudaError_t launch_embed_ln(const DevTable & word, const float * postype, const 
 cudaError_t launch_ln(const __half * x, const float * gamma, const float * beta, int T, int H,
                       __half * out, __half * out_fq, int fq_type, cudaStream_t st) {
     if (T <= 0) return cudaSuccess;
-    ln_kernel<<<(T + ROWS_PER_CTA - 1) / ROWS_PER_CTA, ROWS_PER_CTA * 32, 0, st>>>(
-        x, gamma, beta, T, H, out, out_fq, fq_type);
+    const int grid = (T + ROWS_PER_CTA - 1) / ROWS_PER_CTA;
+    const int nch = (H / 8 + 31) / 32;
+    if (nch <= 1) ln_kernel<1><<<grid, ROWS_PER_CTA * 32, 0, st>>>(x, gamma, beta, T, H, out, out_fq, fq_type);
+    else if (nch == 2) ln_kernel<2><<<grid, ROWS_PER_CTA * 32, 0, st>>>(x, gamma, beta, T, H, out, out_fq, fq_type);
+    else if (nch == 3) ln_kernel<3><<<grid, ROWS_PER_CTA * 32, 0, st>>>(x, gamma, beta, T, H, out, out_fq, fq_type);
+    else ln_kernel<4><<<grid, ROWS_PER_CTA * 32, 0, st>>>(x, gamma, beta, T, H, out, out_fq, fq_type);
     return cudaGetLastError();
 }
 
