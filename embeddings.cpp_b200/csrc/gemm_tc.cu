@@ -9,7 +9,7 @@
 //   warp 1      MMA issuer: one elected lane issues tcgen05.mma kind::f16 (M=128, N=BN,
 //               K=16) x4 per k-stage, accumulators double-buffered in TMEM
 //   warps 2-5   epilogue: tcgen05.ld -> bias/GELU/residual/fake-quant -> fp16 -> global
-//   warps 6-9   (q4 weights only) dequantise the BN x 64 weight stage straight from the
+//   warps 6-13  (q4 weights only) dequantise the BN x 64 weight stage straight from the
 //               4-bit planes in HBM/L2 into the swizzled smem B tile, so the weights
 //               cross HBM once at 4.5 / 5 bits (reference block formats ggml.c:893-907,
 //               dequant rule ggml.c:1524-1563)
@@ -90,21 +90,26 @@ template <int N> __device__ __forceinline__ void tma_store_wait_all() {
     asm volatile("cp.async.bulk.wait_group %0;" :: "n"(N) : "memory");
 }
 
-// two nibbles -> two fp16 weights.  `w` holds e(2i) at bits [4i,4i+4), e(2i+1) at [16+4i,..)
+constexpr int DQ_WARPS = 8;          // q4 dequant producer warps (two per SM sub-partition)
+
+// two nibbles -> two fp16 weights.  `w` holds e(2i) at bits [4i,4i+4), e(2i+1) at [16+4i,..).
+// The nibble is OR-ed into the mantissa of an fp16 constant whose ulp matches the nibble's
+// bit position (1024 for mantissa bits 0-3, 64 for bits 4-7), so a word needs one shift for its
+// four pairs; then (q - 8) * d  or  q * d + m  in half2.
 template <int WT>
 __device__ __forceinline__ uint32_t dq_pair(uint32_t w, int i, __half2 d2, __half2 m2) {
-    uint32_t x = ((w >> (4 * i)) & 0x000F000Fu) | 0x64006400u;        // fp16 1024 + q
-    __half2 h = *reinterpret_cast<__half2 *>(&x);
-    if (WT == W_Q4_0) {
-        h = __hmul2(__hsub2(h, __half2half2(__ushort_as_half((unsigned short) 0x6408))), d2);   // (q-8)*d
-    } else {
-        h = __hfma2(__hsub2(h, __half2half2(__ushort_as_half((unsigned short) 0x6400))), d2, m2); // q*d+m
-    }
+    uint32_t x;
+    unsigned short base;                 // fp16 bits of (magic + 8) for q4_0, magic for q4_1
+    const uint32_t ws = i < 2 ? w : (w >> 8);                       // one shift serves pairs 2 and 3
+    if ((i & 1) == 0) { x = (ws & 0x000F000Fu) | 0x64006400u; base = WT == W_Q4_0 ? 0x6408 : 0x6400; }   // 1024 + q
+    else              { x = (ws & 0x00F000F0u) | 0x54005400u; base = WT == W_Q4_0 ? 0x5480 : 0x5400; }   //   64 + q
+    __half2 h = __hsub2(*reinterpret_cast<__half2 *>(&x), __half2half2(__ushort_as_half(base)));
+    h = WT == W_Q4_0 ? __hmul2(h, d2) : __hfma2(h, d2, m2);
     return *reinterpret_cast<uint32_t *>(&h);
 }
 
 template <int BN, int WT>
-__global__ void __launch_bounds__(WT == W_F16 ? 192 : 320, 1)
+__global__ void __launch_bounds__(WT == W_F16 ? 192 : 192 + 32 * DQ_WARPS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const __grid_constant__ CUtensorMap tmap_out, const GemmParams p) {
     using Cfg = GemmCfg<BN>;
@@ -132,7 +137,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         if (WT == W_F16) tma_prefetch_desc(&tmap_b);
         tma_prefetch_desc(&tmap_out);
         for (int s = 0; s < S; ++s) {
-            mbar_init(&full[s], WT == W_F16 ? 1 : 1 + 4);
+            mbar_init(&full[s], WT == W_F16 ? 1 : 1 + DQ_WARPS);
             mbar_init(&empty[s], 1);
         }
         for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 4); }
@@ -281,10 +286,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         }
         if (lane == 0) tma_store_wait_all<0>();
     } else {
-        // ------------------------------------------------------------ q4 dequant producers (4 warps)
+        // ------------------------------------------------------------ q4 dequant producers
         if (WT != W_F16) {
-            const int t = threadIdx.x - 192;                     // 0..127
-            constexpr int UNITS = BN * 2 / 128;                  // 32-weight blocks per thread per stage
+            constexpr int DQT = 32 * DQ_WARPS;
+            const int t = threadIdx.x - 192;                     // 0..DQT-1
+            constexpr int UNITS = (BN * 2 + DQT - 1) / DQT;      // 32-weight blocks per thread per stage
             int s = 0; uint32_t ph = 0;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
                 const int n0 = (tile % num_n) * BN;
@@ -294,16 +300,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     uint4 nib[UNITS]; __half d[UNITS], m[UNITS];
 #pragma unroll
                     for (int u = 0; u < UNITS; ++u) {
-                        const size_t b = blk0 + t + 128 * u;
-                        nib[u] = __ldg(p.qnib + b);
-                        d[u] = __ldg(p.qd + b);
-                        m[u] = WT == W_Q4_1 ? __ldg(p.qm + b) : __half();
+                        if (t + DQT * u < BN * 2) {
+                            const size_t b = blk0 + t + DQT * u;
+                            nib[u] = __ldg(p.qnib + b);
+                            d[u] = __ldg(p.qd + b);
+                            m[u] = WT == W_Q4_1 ? __ldg(p.qm + b) : __half();
+                        }
                     }
                     mbar_wait(&empty[s], ph ^ 1);
                     uint8_t * bt = smem_b + s * Cfg::kBBytes;
 #pragma unroll
                     for (int u = 0; u < UNITS; ++u) {
-                        const int unit = t + 128 * u;
+                        const int unit = t + DQT * u;
+                        if (unit >= BN * 2) continue;
                         const int r = unit >> 1, half_k = unit & 1;          // row in tile, which 32-block
                         const __half2 d2 = __half2half2(d[u]), m2 = __half2half2(m[u]);
                         const uint32_t w[4] = {nib[u].x, nib[u].y, nib[u].z, nib[u].w};
@@ -345,7 +354,7 @@ static cudaError_t launch_one(const GemmArgs & g, int num_sms, cudaStream_t st) 
     const int tiles = ((g.M + BM - 1) / BM) * (w.N / BN);
     const int grid = tiles < num_sms ? tiles : num_sms;
     if (grid <= 0) return cudaSuccess;
-    kern<<<grid, WT == W_F16 ? 192 : 320, Cfg::kSmemBytes, st>>>(*g.tmap_a, w.tmap, *g.tmap_out, p);
+    kern<<<grid, WT == W_F16 ? 192 : 192 + 32 * DQ_WARPS, Cfg::kSmemBytes, st>>>(*g.tmap_a, w.tmap, *g.tmap_out, p);
     return cudaGetLastError();
 }
 
