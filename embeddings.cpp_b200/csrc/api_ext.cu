@@ -178,7 +178,7 @@ static int32_t gemm_test_impl(int32_t M, int32_t N, int32_t K, int32_t wtype, in
         if (!wbuf.alloc(hw.size() * 2)) return -3;
         cudaMemcpy(wbuf.p, hw.data(), hw.size() * 2, cudaMemcpyHostToDevice);
         w.w16 = wbuf.as<__half>();
-        if (!make_tmap_f16_2d(&w.tmap, w.w16, N, K, w.bn)) return -4;
+        if (!make_tmap_f16_2d(&w.tmap, w.w16, N, K, w.bn / 2)) return -4;
     } else {
         // random raw blocks in the FILE layout, repacked by the production upload kernel
         const int bs = wtype == W_Q4_0 ? 18 : 20;
@@ -198,11 +198,12 @@ static int32_t gemm_test_impl(int32_t M, int32_t N, int32_t K, int32_t wtype, in
         w.qnib = nib.as<uint4>(); w.qd = qd.as<__half>(); w.qm = wtype == W_Q4_1 ? qm.as<__half>() : nullptr;
         memset(&w.tmap, 0, sizeof(w.tmap));
     }
-    CUtensorMap tma, tmo;
+    CUtensorMap tma, tmo, tmr;
     if (!make_tmap_f16_2d(&tma, a.p, rows, K, 128)) return -4;
+    if (!make_tmap_f16_2d(&tmr, res.p, M, N, 32)) return -4;
     if (!make_tmap_f16_2d(&tmo, o1.p, M, N, 32)) return -4;        // exactly M rows: the store must clip the tail tile
     const int fq = wtype == W_Q4_1 ? W_Q4_1 : W_Q4_0;
-    GemmArgs g1{&tma, &tmo, a.as<__half>(), &w, res.as<__half>(), o1.as<__half>(), M, epilogue, fq};
+    GemmArgs g1{&tma, &tmo, &tmr, a.as<__half>(), &w, res.as<__half>(), o1.as<__half>(), M, epilogue, fq};
     GemmArgs g2 = g1; g2.out = o2.as<__half>();
     if (!cuda_ok(launch_gemm_tc(g1, prop.multiProcessorCount, 0), "selftest gemm_tc launch")) return -6;
     if (!cuda_ok(cudaDeviceSynchronize(), "selftest gemm_tc")) return -6;

@@ -47,6 +47,7 @@ struct Replica {
            * x1 = nullptr, * x1q = nullptr, * mid = nullptr;
     CUtensorMap tm_xin, tm_ctx, tm_x1in, tm_mid;     // A-operand maps (box 64 x 128)
     CUtensorMap to_qkv, to_y, to_mid;                // output maps (box 64 x 32, epilogue TMA stores)
+    CUtensorMap tr_x, tr_x1;                         // residual maps (box 64 x 32, epilogue TMA loads)
     static const int kSlots = 2;
     int32_t * d_ids[kSlots] = {nullptr, nullptr};    // [t_cap]
     int32_t * d_cu[kSlots] = {nullptr, nullptr};     // [b_cap+1]

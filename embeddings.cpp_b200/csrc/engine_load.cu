@@ -110,7 +110,7 @@ bool build_weight(Replica & r, DevWeight & w, const TensorEntry * const * parts,
             if (!cuda_ok(cudaMemcpyAsync(bias + n_off, biases[i]->data, biases[i]->nbytes, cudaMemcpyHostToDevice, r.stream), "H2D bias")) return false;
             n_off += (int) t.ne[1];
         }
-        if (!make_tmap_f16_2d(&w.tmap, w16, (uint64_t) N, (uint64_t) K, (uint32_t) w.bn)) {
+        if (!make_tmap_f16_2d(&w.tmap, w16, (uint64_t) N, (uint64_t) K, (uint32_t) w.bn / 2)) {
             fprintf(stderr, "bert_load_from_file: cuTensorMapEncodeTiled failed for a weight map\n");
             return false;
         }
@@ -332,7 +332,8 @@ bool Engine::alloc_workspace(Replica & r) {
     if (!make_tmap_f16_2d(&r.tm_xin, r.xq, rows, H, 128) || !make_tmap_f16_2d(&r.tm_ctx, r.ctx, rows, H, 128) ||
         !make_tmap_f16_2d(&r.tm_x1in, r.x1q, rows, H, 128) || !make_tmap_f16_2d(&r.tm_mid, r.mid, rows, I, 128) ||
         !make_tmap_f16_2d(&r.to_qkv, r.qkv, rows, 3 * H, 32) || !make_tmap_f16_2d(&r.to_y, r.y, rows, H, 32) ||
-        !make_tmap_f16_2d(&r.to_mid, r.mid, rows, I, 32)) {
+        !make_tmap_f16_2d(&r.to_mid, r.mid, rows, I, 32) ||
+        !make_tmap_f16_2d(&r.tr_x, r.x, rows, H, 32) || !make_tmap_f16_2d(&r.tr_x1, r.x1, rows, H, 32)) {
         fprintf(stderr, "bert_load_from_file: cuTensorMapEncodeTiled failed for an activation map\n");
         return false;
     }

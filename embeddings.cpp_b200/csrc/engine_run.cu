@@ -45,8 +45,8 @@ bool Engine::forward(Replica & r, const int32_t * d_ids, const int32_t * d_cu, i
     auto end = [&]() { if (r.profiling) cudaEventRecord(r.spans.back().b, st); };
 
     auto gemm = [&](const CUtensorMap * tm, const CUtensorMap * tmo, const __half * a, const DevWeight & w,
-                    const __half * res, __half * out, int epi) {
-        GemmArgs g{tm, tmo, a, &w, res, out, T, epi, fq_type};
+                    const __half * res, const CUtensorMap * tmr, __half * out, int epi) {
+        GemmArgs g{tm, tmo, tmr, a, &w, res, out, T, epi, fq_type};
         begin(KK_GEMM);
         L(KK_GEMM, gemm_simt ? launch_gemm_simt(g, st) : launch_gemm_tc(g, r.num_sms, st), "gemm");
         end();
@@ -58,17 +58,17 @@ bool Engine::forward(Replica & r, const int32_t * d_ids, const int32_t * d_cu, i
     end();
     for (int il = 0; il < hp.n_layer && L.ok; ++il) {
         const LayerDev & ly = r.layers[il];
-        gemm(&r.tm_xin, &r.to_qkv, r.xq, ly.qkv, nullptr, r.qkv, EPI_BIAS);
+        gemm(&r.tm_xin, &r.to_qkv, r.xq, ly.qkv, nullptr, nullptr, r.qkv, EPI_BIAS);
         begin(KK_ATTN);
         L(KK_ATTN, (attn_ref ? launch_attention_ref : launch_attention)(r.qkv, d_cu, n_sent, max_len, hp.n_head,
                                                                          H / hp.n_head, r.ctx, fq_type, st), "attention");
         end();
-        gemm(&r.tm_ctx, &r.to_y, r.ctx, ly.o, r.x, r.y, EPI_BIAS | EPI_RESIDUAL);
+        gemm(&r.tm_ctx, &r.to_y, r.ctx, ly.o, r.x, &r.tr_x, r.y, EPI_BIAS | EPI_RESIDUAL);
         begin(KK_LN);
         L(KK_LN, launch_ln(r.y, ly.ln_att_g, ly.ln_att_b, T, H, r.x1, fq ? r.x1q : nullptr, fq_type, st), "ln_att");
         end();
-        gemm(&r.tm_x1in, &r.to_mid, r.x1q, ly.ffi, nullptr, r.mid, EPI_BIAS | EPI_GELU | (fq ? EPI_FAKEQUANT : 0));
-        gemm(&r.tm_mid, &r.to_y, r.mid, ly.ffo, r.x1, r.y, EPI_BIAS | EPI_RESIDUAL);
+        gemm(&r.tm_x1in, &r.to_mid, r.x1q, ly.ffi, nullptr, nullptr, r.mid, EPI_BIAS | EPI_GELU | (fq ? EPI_FAKEQUANT : 0));
+        gemm(&r.tm_mid, &r.to_y, r.mid, ly.ffo, r.x1, &r.tr_x1, r.y, EPI_BIAS | EPI_RESIDUAL);
         begin(KK_LN);
         L(KK_LN, launch_ln(r.y, ly.ln_out_g, ly.ln_out_b, T, H, r.x, fq ? r.xq : nullptr, fq_type, st), "ln_out");
         end();

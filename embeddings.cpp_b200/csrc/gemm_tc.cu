@@ -18,24 +18,29 @@
 
 namespace b200 {
 
-constexpr int BM = 128;
+constexpr int BM = 128;          // rows per CTA; a CTA pair computes a 256 x BN tile
 constexpr int BK = 64;
 constexpr int UMMA_K = 16;
+constexpr int kSmemLimit = 232448;                   // 227 KB opt-in limit per CTA
 
 template <int BN> struct GemmCfg {
-    static constexpr int kStages   = BN >= 192 ? 4 : 6;
+    static constexpr int kBHalf    = BN / 2;                 // B rows this CTA supplies
     static constexpr int kABytes   = BM * BK * 2;
-    static constexpr int kBBytes   = BN * BK * 2;
+    static constexpr int kBBytes   = kBHalf * BK * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
     static constexpr int kTmemCols = (2 * BN <= 128) ? 128 : (2 * BN <= 256 ? 256 : 512);
     static constexpr int kAccStride = BN <= 64 ? 64 : (BN <= 128 ? 128 : 256);
     static constexpr int kOutBytes = 4 * 2 * 4096;      // 4 epilogue warps x 2 buffers x [32 rows][128 B]
-    static constexpr int kSmemBytes = kStages * kStageBytes + kOutBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+    static constexpr int kResBytes = 4 * 2 * 4096;      // same geometry, residual boxes prefetched by TMA
+    static constexpr int kFixed = kOutBytes + kResBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+    static constexpr int kStagesFit = (kSmemLimit - kFixed) / kStageBytes;
+    static constexpr int kStages   = kStagesFit > 6 ? 6 : kStagesFit;
+    static constexpr int kSmemBytes = kStages * kStageBytes + kFixed;
 };
 
 struct GemmParams {
     const uint4 * qnib; const __half * qd; const __half * qm;
-    const float * bias; const __half * residual; __half * out;
+    const float * bias; __half * out;
     int M, N, K, epilogue, fq_type;
 };
 
@@ -108,130 +113,160 @@ __device__ __forceinline__ uint32_t dq_pair(uint32_t w, int i, __half2 d2, __hal
     return *reinterpret_cast<uint32_t *>(&h);
 }
 
+// Tile walk shared by all roles: cluster `cid` of `ncl` takes tiles cid, cid + ncl, ...;
+// tile -> (m block of 256 rows, n block of BN columns), n fastest so that concurrently
+// running clusters share A rows through L2.
+struct TileWalk {
+    int num_n, num_tiles, cid, ncl;
+    __device__ __forceinline__ int my_tiles() const { return cid < num_tiles ? (num_tiles - cid + ncl - 1) / ncl : 0; }
+    __device__ __forceinline__ int tile(int i) const { return cid + i * ncl; }
+};
+
 template <int BN, int WT>
-__global__ void __launch_bounds__(WT == W_F16 ? 192 : 192 + 32 * DQ_WARPS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(WT == W_F16 ? 192 : 192 + 32 * DQ_WARPS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-               const __grid_constant__ CUtensorMap tmap_out, const GemmParams p) {
+               const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
+               const GemmParams p) {
     using Cfg = GemmCfg<BN>;
     constexpr int S = Cfg::kStages;
+    constexpr int NB = BN / 64;                               // 64-column output boxes per tile
     extern __shared__ uint8_t smem_raw[];
     uint8_t * smem = (uint8_t *) (((uintptr_t) smem_raw + 1023) & ~(uintptr_t) 1023);
     uint8_t * smem_a = smem;                                  // S x 16 KB
-    uint8_t * smem_b = smem + S * Cfg::kABytes;               // S x BN*128 B
+    uint8_t * smem_b = smem + S * Cfg::kABytes;               // S x (BN/2)*128 B
     uint8_t * smem_out = smem + S * Cfg::kStageBytes;         // 4 warps x 2 x 4 KB staging for TMA stores
-    uint64_t * bars = (uint64_t *) (smem + S * Cfg::kStageBytes + Cfg::kOutBytes);
-    uint64_t * full = bars;                 // [S]
-    uint64_t * empty = bars + S;            // [S]
-    uint64_t * tfull = bars + 2 * S;        // [2]
-    uint64_t * tempty = bars + 2 * S + 2;   // [2]
-    uint32_t * tmem_slot = (uint32_t *) (bars + 2 * S + 4);
+    uint8_t * smem_res = smem_out + Cfg::kOutBytes;           // 4 warps x 2 x 4 KB residual boxes
+    uint64_t * bars = (uint64_t *) (smem_res + Cfg::kResBytes);
+    uint64_t * full = bars;                 // [S]   leader's copy is the live one
+    uint64_t * empty = bars + S;            // [S]   per CTA, signalled by the multicast commit
+    uint64_t * tfull = bars + 2 * S;        // [2]   per CTA, multicast commit
+    uint64_t * tempty = bars + 2 * S + 2;   // [2]   leader's copy is live: 8 epilogue warps arrive
+    uint64_t * rfull = bars + 2 * S + 4;    // [4][2] residual boxes, per epilogue warp
+    uint32_t * tmem_slot = (uint32_t *) (bars + 2 * S + 12);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int num_n = p.N / BN;
-    const int num_m = (p.M + BM - 1) / BM;
-    const int num_tiles = num_m * num_n;
+    const uint32_t rank = cluster_ctarank();                  // 0 = leader (issues the MMAs)
+    TileWalk tw;
+    tw.num_n = p.N / BN;
+    tw.num_tiles = ((p.M + 2 * BM - 1) / (2 * BM)) * tw.num_n;
+    tw.cid = (int) cluster_id_x();
+    tw.ncl = (int) cluster_nctaid_x();
+    const int my_tiles = tw.my_tiles();
     const int num_k = p.K / BK;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmap_a);
         if (WT == W_F16) tma_prefetch_desc(&tmap_b);
         tma_prefetch_desc(&tmap_out);
+        if (p.epilogue & EPI_RESIDUAL) tma_prefetch_desc(&tmap_res);
         for (int s = 0; s < S; ++s) {
-            mbar_init(&full[s], WT == W_F16 ? 1 : 1 + DQ_WARPS);
+            mbar_init(&full[s], WT == W_F16 ? 1 : 1 + 2 * DQ_WARPS);
             mbar_init(&empty[s], 1);
         }
-        for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 4); }
+        for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 8); }
+        for (int i = 0; i < 8; ++i) mbar_init(&rfull[i], 1);
         fence_mbar_init();
     }
-    if (warp == 1) { tmem_alloc(tmem_slot, Cfg::kTmemCols); tmem_relinquish(); }
+    if (warp == 1) { tmem_alloc_pair(tmem_slot, Cfg::kTmemCols); tmem_relinquish_pair(); }
     tc_fence_before_sync();
     __syncthreads();
+    cluster_sync_all();                     // the peer's barriers exist before anything signals them
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
-        // ------------------------------------------------------------ TMA producer
+        // ------------------------------------------------------------ TMA producer (both CTAs)
         if (lane == 0) {
+            const uint32_t full_leader = mapa_u32(smem_u32(&full[0]), 0);
             int s = 0; uint32_t ph = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const int m0 = (tile / num_n) * BM, n0 = (tile % num_n) * BN;
+            for (int i = 0; i < my_tiles; ++i) {
+                const int tile = tw.tile(i);
+                const int m0 = (tile / tw.num_n) * (2 * BM) + (int) rank * BM;
+                const int nb0 = (tile % tw.num_n) * BN + (int) rank * Cfg::kBHalf;
                 for (int kb = 0; kb < num_k; ++kb) {
                     mbar_wait(&empty[s], ph ^ 1);
-                    mbar_expect_tx(&full[s], WT == W_F16 ? Cfg::kStageBytes : Cfg::kABytes);
-                    tma_load_2d(smem_a + s * Cfg::kABytes, &tmap_a, &full[s], kb * BK, m0);
-                    if (WT == W_F16) tma_load_2d(smem_b + s * Cfg::kBBytes, &tmap_b, &full[s], kb * BK, n0);
+                    if (rank == 0) mbar_expect_tx(&full[s], 2 * (WT == W_F16 ? Cfg::kStageBytes : Cfg::kABytes));
+                    tma_load_2d_pair(smem_a + s * Cfg::kABytes, &tmap_a, full_leader + 8 * s, kb * BK, m0);
+                    if (WT == W_F16) tma_load_2d_pair(smem_b + s * Cfg::kBBytes, &tmap_b, full_leader + 8 * s, kb * BK, nb0);
                     if (++s == S) { s = 0; ph ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
-        // ------------------------------------------------------------ MMA issuer
-        constexpr uint32_t idesc = umma_idesc_f16(BM, BN);
-        int s = 0; uint32_t ph = 0; int it = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-            const int acc = it & 1;
-            const uint32_t acc_ph = (it >> 1) & 1;
-            mbar_wait(&tempty[acc], acc_ph ^ 1);
-            tc_fence_after_sync();
-            const uint32_t d_tmem = tmem_base + acc * Cfg::kAccStride;
-            for (int kb = 0; kb < num_k; ++kb) {
-                mbar_wait(&full[s], ph);
+        // ------------------------------------------------------------ MMA issuer (leader CTA only)
+        if (rank == 0) {
+            constexpr uint32_t idesc = umma_idesc_f16(2 * BM, BN);
+            int s = 0; uint32_t ph = 0;
+            for (int it = 0; it < my_tiles; ++it) {
+                const int acc = it & 1;
+                const uint32_t acc_ph = (it >> 1) & 1;
+                mbar_wait(&tempty[acc], acc_ph ^ 1);
                 tc_fence_after_sync();
-                if (elect_one()) {
-                    const uint64_t adesc = umma_smem_desc_sw128(smem_u32(smem_a + s * Cfg::kABytes));
-                    const uint64_t bdesc = umma_smem_desc_sw128(smem_u32(smem_b + s * Cfg::kBBytes));
+                const uint32_t d_tmem = tmem_base + acc * Cfg::kAccStride;
+                for (int kb = 0; kb < num_k; ++kb) {
+                    mbar_wait(&full[s], ph);
+                    tc_fence_after_sync();
+                    if (elect_one()) {
+                        const uint64_t adesc = umma_smem_desc_sw128(smem_u32(smem_a + s * Cfg::kABytes));
+                        const uint64_t bdesc = umma_smem_desc_sw128(smem_u32(smem_b + s * Cfg::kBBytes));
 #pragma unroll
-                    for (int k = 0; k < BK / UMMA_K; ++k) {
-                        // +32 B per K=16 step inside the 128-B swizzle row (address field is >>4)
-                        umma_f16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+                        for (int k = 0; k < BK / UMMA_K; ++k) {
+                            // +32 B per K=16 step inside the 128-B swizzle row (address field is >>4)
+                            umma_f16_ss_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+                        }
+                        umma_commit_pair(&empty[s]);                          // frees the stage in both CTAs
+                        if (kb == num_k - 1) umma_commit_pair(&tfull[acc]);   // accumulators ready in both CTAs
                     }
-                    umma_commit(&empty[s]);                      // frees the smem stage
-                    if (kb == num_k - 1) umma_commit(&tfull[acc]);   // accumulator ready
+                    __syncwarp();
+                    if (++s == S) { s = 0; ph ^= 1; }
                 }
-                __syncwarp();
-                if (++s == S) { s = 0; ph ^= 1; }
             }
         }
     } else if (warp < 6) {
-        // ------------------------------------------------------------ epilogue (4 warps)
-        // Per 64-column box: (residual: coalesced LDG -> swizzled smem) ; TMEM -> registers ;
-        // bias / GELU / + residual (own row from smem) / q8 fake-quant ; fp16 -> swizzled smem ;
-        // one TMA store of the warp's [32 rows x 64 cols] sub-box.  Global traffic is whole
-        // 128-B rows in both directions; everything is warp-local (no CTA barrier).
+        // ------------------------------------------------------------ epilogue (4 warps per CTA)
+        // Per 64-column box: TMEM -> registers ; bias / GELU / + residual (own row of the box the
+        // warp prefetched by TMA) / q8 fake-quant ; fp16 -> swizzled smem ; one TMA store of the
+        // warp's [32 rows x 64 cols] sub-box.  Global traffic is whole 128-B rows in both
+        // directions; everything is warp-local (no CTA barrier).
         const int q = warp & 3;                    // TMEM lane quadrant this warp may access
-        uint8_t * stage_base = smem_out + (warp - 2) * 2 * 4096;
-        int it = 0;
-        uint32_t box_ctr = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-            const int m0 = (tile / num_n) * BM, n0 = (tile % num_n) * BN;
+        uint8_t * out_base = smem_out + (warp - 2) * 2 * 4096;
+        uint8_t * res_base = smem_res + (warp - 2) * 2 * 4096;
+        uint64_t * rbar = rfull + (warp - 2) * 2;
+        const uint32_t tempty_leader = mapa_u32(smem_u32(&tempty[0]), 0);
+        const bool has_res = (p.epilogue & EPI_RESIDUAL) != 0;
+        const int total_boxes = my_tiles * NB;
+        auto box_coords = [&](int j, int & c0, int & row0) {
+            const int tile = tw.tile(j / NB);
+            c0 = (tile % tw.num_n) * BN + (j % NB) * 64;
+            row0 = (tile / tw.num_n) * (2 * BM) + (int) rank * BM + q * 32;
+        };
+        if (has_res && lane == 0 && total_boxes > 0) {
+            int c0, row0; box_coords(0, c0, row0);
+            mbar_expect_tx(&rbar[0], 4096);
+            tma_load_2d(res_base, &tmap_res, &rbar[0], c0, row0);
+        }
+        int j = 0;
+        for (int it = 0; it < my_tiles; ++it) {
             const int acc = it & 1;
             const uint32_t acc_ph = (it >> 1) & 1;
-            const int wrow0 = m0 + q * 32;                  // first row of this warp's sub-tile
             mbar_wait(&tfull[acc], acc_ph);
             tc_fence_after_sync();
 #pragma unroll 1
-            for (int b = 0; b < BN / 64; ++b, ++box_ctr) {
-                uint8_t * st = stage_base + (box_ctr & 1) * 4096;
-                const int c0 = n0 + b * 64;
+            for (int b = 0; b < NB; ++b, ++j) {
+                uint8_t * st = out_base + (j & 1) * 4096;
+                const uint8_t * rs = res_base + (j & 1) * 4096;
+                int c0, wrow0; box_coords(j, c0, wrow0);
                 // the TMA store that last read this buffer (two boxes ago) must be done reading
                 if (lane == 0) tma_store_wait_read<1>();
-                __syncwarp();
-                if (p.epilogue & EPI_RESIDUAL) {
-                    uint4 rr[8];
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const int id = lane + 32 * i, r = id >> 3, c = id & 7;
-                        rr[i] = (wrow0 + r < p.M)
-                            ? __ldg(reinterpret_cast<const uint4 *>(p.residual + (size_t) (wrow0 + r) * p.N + c0) + c)
-                            : make_uint4(0, 0, 0, 0);
+                if (has_res) {
+                    if (lane == 0 && j + 1 < total_boxes) {       // prefetch the next box's residual
+                        int c1, r1; box_coords(j + 1, c1, r1);
+                        mbar_expect_tx(&rbar[(j + 1) & 1], 4096);
+                        tma_load_2d(res_base + ((j + 1) & 1) * 4096, &tmap_res, &rbar[(j + 1) & 1], c1, r1);
                     }
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const int id = lane + 32 * i, r = id >> 3, c = id & 7;
-                        *reinterpret_cast<uint4 *>(st + r * 128 + ((c ^ (r & 7)) << 4)) = rr[i];
-                    }
-                    __syncwarp();
+                    mbar_wait(&rbar[j & 1], (j >> 1) & 1);
                 }
+                __syncwarp();
 #pragma unroll
                 for (int hh = 0; hh < 2; ++hh) {
                     uint32_t r[32];
@@ -252,11 +287,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 #pragma unroll
                         for (int i = 0; i < 16; ++i) v[i] = gelu2_ref_numerics(v[i]);
                     }
-                    if (p.epilogue & EPI_RESIDUAL) {
+                    if (has_res) {
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
                             const int c = hh * 4 + i;
-                            const uint4 u = *reinterpret_cast<const uint4 *>(st + lane * 128 + ((c ^ (lane & 7)) << 4));
+                            const uint4 u = *reinterpret_cast<const uint4 *>(rs + lane * 128 + ((c ^ (lane & 7)) << 4));
                             const __half2 * h = reinterpret_cast<const __half2 *>(&u);
 #pragma unroll
                             for (int e = 0; e < 4; ++e) v[i * 4 + e] = __fadd2_rn(v[i * 4 + e], __half22float2(h[e]));
@@ -282,55 +317,78 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             }
             tc_fence_before_sync();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty[acc]);
+            if (lane == 0) mbar_arrive_cluster(tempty_leader + 8 * acc);
         }
         if (lane == 0) tma_store_wait_all<0>();
     } else {
-        // ------------------------------------------------------------ q4 dequant producers
+        // ------------------------------------------------------------ q4 dequant producers (both CTAs)
+        // Each CTA dequantises the BN/2 weight rows it contributes to the pair's B operand.  The
+        // 4-bit loads run two k-stages ahead of the stage being written (register ring), so the
+        // L2 latency is off the critical path.
         if (WT != W_F16) {
             constexpr int DQT = 32 * DQ_WARPS;
+            constexpr int NUNIT = BN;                            // 32-weight blocks per CTA per stage
+            constexpr int UNITS = (NUNIT + DQT - 1) / DQT;       // per thread
             const int t = threadIdx.x - 192;                     // 0..DQT-1
-            constexpr int UNITS = (BN * 2 + DQT - 1) / DQT;      // 32-weight blocks per thread per stage
-            int s = 0; uint32_t ph = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const int n0 = (tile % num_n) * BN;
-                for (int kb = 0; kb < num_k; ++kb) {
-                    // stage kb of rows n0..n0+BN-1 is contiguous: [kb][n][2] blocks
-                    const size_t blk0 = ((size_t) kb * p.N + n0) * 2;
-                    uint4 nib[UNITS]; __half d[UNITS], m[UNITS];
+            const uint32_t full_leader = mapa_u32(smem_u32(&full[0]), 0);
+            struct Regs { uint4 nib[UNITS]; __half d[UNITS], m[UNITS]; };
+            const int total = my_tiles * num_k;
+            int ld_i = 0, ld_kb = 0, ld_it = 0;                  // load cursor: iteration, its k-stage, its tile slot
+            auto load = [&](Regs & R) {
+                if (ld_i < total) {
+                    const int tile = tw.tile(ld_it);
+                    const int nb0 = (tile % tw.num_n) * BN + (int) rank * Cfg::kBHalf;
+                    // stage kb of rows nb0..nb0+BN/2-1 is contiguous: [kb][n][2] blocks
+                    const size_t blk0 = ((size_t) ld_kb * p.N + nb0) * 2;
 #pragma unroll
                     for (int u = 0; u < UNITS; ++u) {
-                        if (t + DQT * u < BN * 2) {
+                        if (t + DQT * u < NUNIT) {
                             const size_t b = blk0 + t + DQT * u;
-                            nib[u] = __ldg(p.qnib + b);
-                            d[u] = __ldg(p.qd + b);
-                            m[u] = WT == W_Q4_1 ? __ldg(p.qm + b) : __half();
+                            R.nib[u] = __ldg(p.qnib + b);
+                            R.d[u] = __ldg(p.qd + b);
+                            R.m[u] = WT == W_Q4_1 ? __ldg(p.qm + b) : __half();
                         }
                     }
-                    mbar_wait(&empty[s], ph ^ 1);
-                    uint8_t * bt = smem_b + s * Cfg::kBBytes;
+                    ++ld_i;
+                    if (++ld_kb == num_k) { ld_kb = 0; ++ld_it; }
+                }
+            };
+            int s = 0; uint32_t ph = 0;
+            auto emit = [&](const Regs & R) {
+                mbar_wait(&empty[s], ph ^ 1);
+                uint8_t * bt = smem_b + s * Cfg::kBBytes;
 #pragma unroll
-                    for (int u = 0; u < UNITS; ++u) {
-                        const int unit = t + DQT * u;
-                        if (unit >= BN * 2) continue;
-                        const int r = unit >> 1, half_k = unit & 1;          // row in tile, which 32-block
-                        const __half2 d2 = __half2half2(d[u]), m2 = __half2half2(m[u]);
-                        const uint32_t w[4] = {nib[u].x, nib[u].y, nib[u].z, nib[u].w};
+                for (int u = 0; u < UNITS; ++u) {
+                    const int unit = t + DQT * u;
+                    if (unit >= NUNIT) continue;
+                    const int r = unit >> 1, half_k = unit & 1;          // row in this CTA's half, which 32-block
+                    const __half2 d2 = __half2half2(R.d[u]), m2 = __half2half2(R.m[u]);
+                    const uint32_t w[4] = {R.nib[u].x, R.nib[u].y, R.nib[u].z, R.nib[u].w};
 #pragma unroll
-                        for (int c = 0; c < 4; ++c) {
-                            uint4 o;
-                            o.x = dq_pair<WT>(w[c], 0, d2, m2);
-                            o.y = dq_pair<WT>(w[c], 1, d2, m2);
-                            o.z = dq_pair<WT>(w[c], 2, d2, m2);
-                            o.w = dq_pair<WT>(w[c], 3, d2, m2);
-                            const int chunk = half_k * 4 + c;
-                            *reinterpret_cast<uint4 *>(bt + r * 128 + ((chunk ^ (r & 7)) << 4)) = o;
-                        }
+                    for (int c = 0; c < 4; ++c) {
+                        uint4 o;
+                        o.x = dq_pair<WT>(w[c], 0, d2, m2);
+                        o.y = dq_pair<WT>(w[c], 1, d2, m2);
+                        o.z = dq_pair<WT>(w[c], 2, d2, m2);
+                        o.w = dq_pair<WT>(w[c], 3, d2, m2);
+                        const int chunk = half_k * 4 + c;
+                        *reinterpret_cast<uint4 *>(bt + r * 128 + ((chunk ^ (r & 7)) << 4)) = o;
                     }
-                    fence_proxy_async_smem();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&full[s]);
-                    if (++s == S) { s = 0; ph ^= 1; }
+                }
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) mbar_arrive_cluster(full_leader + 8 * s);
+                if (++s == S) { s = 0; ph ^= 1; }
+            };
+            Regs r0, r1;
+            load(r0);
+            load(r1);
+            for (int i = 0; i < total; i += 2) {
+                emit(r0);
+                load(r0);
+                if (i + 1 < total) {
+                    emit(r1);
+                    load(r1);
                 }
             }
         }
@@ -338,23 +396,52 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 
     tc_fence_before_sync();
     __syncthreads();
-    if (warp == 1) tmem_dealloc(tmem_base, Cfg::kTmemCols);
+    cluster_sync_all();                     // nobody leaves while the peer may still touch this CTA
+    if (warp == 1) tmem_dealloc_pair(tmem_base, Cfg::kTmemCols);
+}
+
+// Persistent grid: as many CTA pairs as the device can keep resident (cached per device).
+template <int BN, int WT>
+static int max_clusters(int device, int num_sms) {
+    static int cached[64] = {0};
+    if (device >= 0 && device < 64 && cached[device] > 0) return cached[device];
+    using Cfg = GemmCfg<BN>;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned) (num_sms & ~1));
+    cfg.blockDim = dim3(WT == W_F16 ? 192 : 192 + 32 * DQ_WARPS);
+    cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, gemm_tc_kernel<BN, WT>, &cfg) != cudaSuccess || n <= 0) {
+        cudaGetLastError();
+        n = num_sms / 2;
+    }
+    if (n > num_sms / 2) n = num_sms / 2;
+    if (device >= 0 && device < 64) cached[device] = n;
+    return n;
 }
 
 template <int BN, int WT>
 static cudaError_t launch_one(const GemmArgs & g, int num_sms, cudaStream_t st) {
     using Cfg = GemmCfg<BN>;
+    static_assert(Cfg::kStages >= 3, "pipeline too shallow");
     auto kern = gemm_tc_kernel<BN, WT>;
-    static bool attr_done = false;     // per instantiation; every device needs it -> set each time cheaply
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
-    (void) attr_done;
     if (e != cudaSuccess) return e;
+    int device = 0;
+    cudaGetDevice(&device);
     const DevWeight & w = *g.w;
-    GemmParams p{w.qnib, w.qd, w.qm, w.bias, g.residual, g.out, g.M, w.N, w.K, g.epilogue, g.fq_type};
-    const int tiles = ((g.M + BM - 1) / BM) * (w.N / BN);
-    const int grid = tiles < num_sms ? tiles : num_sms;
-    if (grid <= 0) return cudaSuccess;
-    kern<<<grid, WT == W_F16 ? 192 : 192 + 32 * DQ_WARPS, Cfg::kSmemBytes, st>>>(*g.tmap_a, w.tmap, *g.tmap_out, p);
+    GemmParams p{w.qnib, w.qd, w.qm, w.bias, g.out, g.M, w.N, w.K, g.epilogue, g.fq_type};
+    const int tiles = ((g.M + 2 * BM - 1) / (2 * BM)) * (w.N / BN);
+    const int ncl_max = max_clusters<BN, WT>(device, num_sms);
+    const int ncl = tiles < ncl_max ? tiles : ncl_max;
+    if (ncl <= 0) return cudaSuccess;
+    if ((g.epilogue & EPI_RESIDUAL) && !g.tmap_res) return cudaErrorInvalidValue;
+    const CUtensorMap * tres = g.tmap_res ? g.tmap_res : g.tmap_out;
+    kern<<<2 * ncl, WT == W_F16 ? 192 : 192 + 32 * DQ_WARPS, Cfg::kSmemBytes, st>>>(*g.tmap_a, w.tmap, *g.tmap_out, *tres, p);
     return cudaGetLastError();
 }
 

@@ -16,7 +16,7 @@ enum : int { EPI_BIAS = 1, EPI_GELU = 2, EPI_RESIDUAL = 4, EPI_FAKEQUANT = 8 };
 
 // A dense weight matrix W[N][K] (K contiguous = the file's ne0, reference bert.cpp:611-623)
 // resident in HBM in its GEMM-ready form:
-//   f32 / f16 files : `w16` fp16 [N][K] row-major (+ TMA map, box 64 x BN)
+//   f32 / f16 files : `w16` fp16 [N][K] row-major (+ TMA map, box 64 x BN/2: each CTA of a pair loads half)
 //   q4_0 / q4_1     : 4-bit planes tiled by 64-wide k-stage so that one stage of any row
 //                     range is contiguous:
 //                       qnib  [K/64][N][2] x 16 B   (nibble order: see repack_q4 in upload.cu)
@@ -38,6 +38,7 @@ struct DevWeight {
 struct GemmArgs {
     const CUtensorMap * tmap_a;     // host pointer to the A map (copied into kernel params)
     const CUtensorMap * tmap_out;   // output map, box {64 cols, 32 rows} (epilogue TMA stores)
+    const CUtensorMap * tmap_res;   // residual map, same geometry (epilogue TMA prefetch) or null
     const __half * a;               // A [M][K] fp16 (used by the SIMT validation kernel only)
     const DevWeight * w;
     const __half * residual;        // [M][N] fp16 or null
