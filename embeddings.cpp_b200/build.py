@@ -18,7 +18,7 @@ LIB = os.path.join(HERE, "lib")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
          "-Xcompiler", "-fPIC,-fvisibility=hidden,-pthread", "-I", os.path.join(HERE, "..", "include")]
-SOURCES = ["gemm_tc.cu", "attention.cu", "rowwise.cu", "upload.cu", "engine_load.cu", "engine_run.cu",
+SOURCES = ["gemm_tc.cu", "attention.cu", "attention_tc.cu", "rowwise.cu", "upload.cu", "engine_load.cu", "engine_run.cu",
            "api.cu", "api_ext.cu", "tokenizer.cpp", "model_file.cpp"]
 
 

@@ -254,12 +254,26 @@ int32_t bertx_selftest_attention(int32_t n_sent, int32_t max_len, int32_t n_head
     const size_t T = (size_t) cu[n_sent];
     std::vector<uint16_t> hq(T * 3 * H);
     for (auto & v : hq) v = f2h_bits(1.5f * nd(rng));
+    if (seed & 1024) {                                             // ramp: K rows grow with the position (forces max rescales)
+        for (int i = 0; i < n_sent; ++i) {
+            for (int t = cu[i]; t < cu[i + 1]; ++t) {
+                const float sc = 0.25f + 3.0f * (float) (t - cu[i]) / (float) (cu[i + 1] - cu[i]);
+                for (int c = H; c < 2 * H; ++c) hq[(size_t) t * 3 * H + c] = f2h_bits(sc * 1.5f * nd(rng));
+            }
+        }
+    }
     DevBuf qkv, dcu, o1, o2;
     if (!qkv.alloc(hq.size() * 2) || !dcu.alloc(cu.size() * 4) || !o1.alloc(T * H * 2) || !o2.alloc(T * H * 2)) return -3;
     cudaMemcpy(qkv.p, hq.data(), hq.size() * 2, cudaMemcpyHostToDevice);
     cudaMemcpy(dcu.p, cu.data(), cu.size() * 4, cudaMemcpyHostToDevice);
     cudaMemset(o1.p, 0xFF, T * H * 2);
-    if (!cuda_ok(launch_attention(qkv.as<__half>(), dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, 0), "selftest attention launch")) return -6;
+    if (d_head == 64 && !(seed & 2048)) {                          // production path for head size 64: tcgen05
+        CUtensorMap tq, tkv;
+        cudaDeviceProp prop; cudaGetDeviceProperties(&prop, 0);
+        if (!make_attention_tmaps(&tq, &tkv, qkv.as<__half>(), T, H)) return -4;
+        if (!cuda_ok(launch_attention_tc(&tq, &tkv, dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1,
+                                         prop.multiProcessorCount, 0), "selftest attention_tc launch")) return -6;
+    } else if (!cuda_ok(launch_attention(qkv.as<__half>(), dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, 0), "selftest attention launch")) return -6;
     if (!cuda_ok(cudaDeviceSynchronize(), "selftest attention")) return -6;
     if (!cuda_ok(launch_attention_ref(qkv.as<__half>(), dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o2.as<__half>(), -1, 0), "selftest attention_ref launch")) return -7;
     if (!cuda_ok(cudaDeviceSynchronize(), "selftest attention_ref")) return -7;

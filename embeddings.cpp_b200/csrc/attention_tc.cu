@@ -1,0 +1,315 @@
+// K2 (tcgen05) -- variable-length fused attention for head size 64:
+//   O = softmax(Q K^T / sqrt(d)) V   per (sentence, head), over the sentence's own tokens only.
+// Replaces the reference's mask build (bert.cpp:957-961), scores + scale + mask + soft_max
+// (bert.cpp:1018-1025, ggml.c:12008-12077) and P*V + permute/cont/cpy (bert.cpp:1027-1036).
+// Nothing of size L x L reaches HBM; padded queries / keys are never stored / always masked.
+//
+// Work item = (sentence, head, 128-query tile); persistent CTAs (two per SM) walk the items
+// round-robin.  Per CTA, warp-specialised:
+//   warp 0     TMA producer: Q tile [128 x 64] once per item, K / V blocks [64 keys x 64] through a
+//              4-stage ring, straight out of the packed qkv activations (128-B swizzle)
+//   warp 1     MMA issuer (one elected lane): S_b = Q K_b^T into a double-buffered TMEM tile
+//              (M=128, N=64), then O += P_b V_b with P read from TMEM (A operand) and V as an
+//              MN-major smem operand -- V is never transposed
+//   warps 2-5  softmax: one query row per thread (tcgen05.ld 32x32b), running max / sum in f32
+//              registers, exp2 on the MUFU, P written back over S as packed fp16 (tcgen05.st).
+//              The running max is only moved (and O rescaled in TMEM) when a block exceeds it by
+//              more than 2^8, so the accumulator normally stays untouched in TMEM until the end.
+// Issue order S_0, S_1, PV_0, S_2, PV_1, ... keeps the tensor pipe one score block ahead of the
+// softmax warps; the second CTA on the SM fills the remaining bubbles.
+#include "kernels.cuh"
+#include "ptx.cuh"
+
+namespace b200 {
+
+namespace {
+
+constexpr int AQ = 128;            // queries per item
+constexpr int AK = 64;             // keys per block
+constexpr int AD = 64;             // head size
+constexpr int KV_STAGES = 4;
+constexpr int ATT_TC_THREADS = 192;
+constexpr int kQBytes = AQ * AD * 2;          // 16 KB
+constexpr int kKVBytes = AK * AD * 2;         // 8 KB each for K and V
+constexpr int kAttSmem = kQBytes + KV_STAGES * 2 * kKVBytes + 1024 /*align*/ + 256 /*barriers*/;
+constexpr uint32_t TM_S = 0;       // S buffers at columns 0 and 64 (P aliases the first 32 columns of each)
+constexpr uint32_t TM_O = 128;     // O accumulator: 64 columns
+constexpr uint32_t TM_COLS = 256;
+constexpr float kRescaleThreshold = 8.f;      // log2 units
+
+struct AttnTcParams {
+    const int32_t * cu;
+    __half * out;
+    int n_sent, n_head, H, max_qt, fq_type;
+    float scale_log2;
+};
+
+struct Item { int t0, len, q0, head; bool valid; };
+
+__device__ __forceinline__ Item decode_item(const AttnTcParams & p, int item) {
+    Item it;
+    const int qt = item % p.max_qt;
+    const int hs = item / p.max_qt;
+    it.head = hs % p.n_head;
+    const int sent = hs / p.n_head;
+    it.t0 = __ldg(p.cu + sent);
+    it.len = __ldg(p.cu + sent + 1) - it.t0;
+    it.q0 = qt * AQ;
+    it.valid = it.q0 < it.len;
+    return it;
+}
+
+__device__ __forceinline__ float ex2f(float x) {
+    float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y;
+}
+__device__ __forceinline__ uint32_t pack_h2(float a, float b) {
+    __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t *>(&h);
+}
+
+__global__ void __launch_bounds__(ATT_TC_THREADS, 2)
+attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv,
+                    const AttnTcParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t * smem = (uint8_t *) (((uintptr_t) smem_raw + 1023) & ~(uintptr_t) 1023);
+    uint8_t * smem_q = smem;
+    uint8_t * smem_k = smem + kQBytes;                               // KV_STAGES x 8 KB
+    uint8_t * smem_v = smem_k + KV_STAGES * kKVBytes;                // KV_STAGES x 8 KB
+    uint64_t * bars = (uint64_t *) (smem_v + KV_STAGES * kKVBytes);
+    uint64_t * q_full = bars;                   // [1]
+    uint64_t * q_empty = bars + 1;              // [1]
+    uint64_t * kv_full = bars + 2;              // [KV_STAGES]
+    uint64_t * kv_empty = kv_full + KV_STAGES;  // [KV_STAGES]
+    uint64_t * s_full = kv_empty + KV_STAGES;   // [2]
+    uint64_t * p_ready = s_full + 2;            // [2]
+    uint64_t * pv_done = p_ready + 2;           // [1]
+    uint64_t * o_free = pv_done + 1;            // [1]
+    uint32_t * tmem_slot = (uint32_t *) (o_free + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int total_items = p.n_sent * p.n_head * p.max_qt;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmap_q);
+        tma_prefetch_desc(&tmap_kv);
+        mbar_init(q_full, 1); mbar_init(q_empty, 1);
+        for (int s = 0; s < KV_STAGES; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(&s_full[a], 1); mbar_init(&p_ready[a], 4); }
+        mbar_init(pv_done, 1);
+        mbar_init(o_free, 4);
+        fence_mbar_init();
+    }
+    if (warp == 1) { tmem_alloc(tmem_slot, TM_COLS); tmem_relinquish(); }
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------ TMA producer
+        if (lane == 0) {
+            uint32_t kv_it = 0, item_n = 0;
+            for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+                const Item it = decode_item(p, item);
+                if (!it.valid) continue;
+                const int nb = (it.len + AK - 1) / AK;
+                mbar_wait(q_empty, (item_n & 1) ^ 1);
+                mbar_expect_tx(q_full, kQBytes);
+                tma_load_2d(smem_q, &tmap_q, q_full, it.head * AD, it.t0 + it.q0);
+                for (int b = 0; b < nb; ++b, ++kv_it) {
+                    const uint32_t st = kv_it % KV_STAGES, ph = (kv_it / KV_STAGES) & 1;
+                    mbar_wait(&kv_empty[st], ph ^ 1);
+                    mbar_expect_tx(&kv_full[st], 2 * kKVBytes);
+                    tma_load_2d(smem_k + st * kKVBytes, &tmap_kv, &kv_full[st], p.H + it.head * AD, it.t0 + b * AK);
+                    tma_load_2d(smem_v + st * kKVBytes, &tmap_kv, &kv_full[st], 2 * p.H + it.head * AD, it.t0 + b * AK);
+                }
+                ++item_n;
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------ MMA issuer
+        constexpr uint32_t idesc_s = umma_idesc_f16(AQ, AK);            // Q (K-major) x K (K-major)
+        constexpr uint32_t idesc_o = umma_idesc_f16(AQ, AD, 1);         // P (TMEM) x V (MN-major)
+        uint32_t g = 0, item_n = 0;                                     // g: running key-block counter
+        for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+            const Item it = decode_item(p, item);
+            if (!it.valid) continue;
+            const int nb = (it.len + AK - 1) / AK;
+            mbar_wait(q_full, item_n & 1);
+            tc_fence_after_sync();
+            for (int b = 0; b <= nb; ++b) {
+                if (b < nb) {
+                    const uint32_t gb = g + b, st = gb % KV_STAGES;
+                    mbar_wait(&kv_full[st], (gb / KV_STAGES) & 1);
+                    tc_fence_after_sync();
+                    if (elect_one()) {
+                        const uint64_t adesc = umma_smem_desc_sw128(smem_u32(smem_q));
+                        const uint64_t bdesc = umma_smem_desc_sw128(smem_u32(smem_k + st * kKVBytes));
+                        const uint32_t d_tmem = tmem_base + TM_S + (gb & 1) * 64;
+#pragma unroll
+                        for (int k = 0; k < AD / 16; ++k) umma_f16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc_s, k != 0);
+                        umma_commit(&s_full[gb & 1]);
+                        if (b == nb - 1) umma_commit(q_empty);          // Q tile may be overwritten
+                    }
+                    __syncwarp();
+                }
+                if (b >= 1) {
+                    const uint32_t gp = g + b - 1, st = gp % KV_STAGES;
+                    mbar_wait(&p_ready[gp & 1], (gp >> 1) & 1);
+                    if (b == 1) mbar_wait(o_free, (item_n & 1) ^ 1);    // previous item's O has been read
+                    tc_fence_after_sync();
+                    if (elect_one()) {
+                        const uint64_t vdesc = umma_smem_desc_sw128_mn(smem_u32(smem_v + st * kKVBytes));
+                        const uint32_t a_tmem = tmem_base + TM_S + (gp & 1) * 64;
+#pragma unroll
+                        for (int k = 0; k < AK / 16; ++k) {
+                            // 16 keys per step: 8 packed columns of P, 16 rows (2 KB) of V
+                            umma_f16_ts(tmem_base + TM_O, a_tmem + 8 * k, vdesc + (uint64_t) (128 * k), idesc_o,
+                                        (b > 1 || k > 0) ? 1u : 0u);
+                        }
+                        umma_commit(&kv_empty[st]);
+                        umma_commit(pv_done);
+                    }
+                    __syncwarp();
+                }
+            }
+            g += nb;
+            ++item_n;
+        }
+    } else {
+        // ------------------------------------------------------------ softmax + output (4 warps)
+        const int q = warp & 3;                               // TMEM lane quadrant of this warp
+        const int row = q * 32 + lane;                        // query row inside the tile
+        const uint32_t lane_base = tmem_base + ((uint32_t) (q * 32) << 16);
+        uint32_t g = 0;
+        for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+            const Item it = decode_item(p, item);
+            if (!it.valid) continue;
+            const int nb = (it.len + AK - 1) / AK;
+            float m_ref = -INFINITY, l = 0.f;
+            for (int b = 0; b < nb; ++b) {
+                const uint32_t gb = g + b;
+                mbar_wait(&s_full[gb & 1], (gb >> 1) & 1);
+                tc_fence_after_sync();
+                const uint32_t s_addr = lane_base + TM_S + (gb & 1) * 64;
+                uint32_t r0[32], r1[32];
+                tmem_ld_32x32b_x32(s_addr, r0);
+                tmem_ld_32x32b_x32(s_addr + 32, r1);
+                tmem_ld_wait();
+                float s[64];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) { s[j] = __uint_as_float(r0[j]); s[32 + j] = __uint_as_float(r1[j]); }
+                const int kvalid = it.len - b * AK;           // keys of this block inside the sentence
+                if (kvalid < AK) {
+#pragma unroll
+                    for (int j = 0; j < 64; ++j) if (j >= kvalid) s[j] = -INFINITY;
+                }
+                float mx = s[0];
+#pragma unroll
+                for (int j = 1; j < 64; ++j) mx = fmaxf(mx, s[j]);
+                mx *= p.scale_log2;
+                // move the reference max only on the first block or when it is exceeded by > 2^8
+                const bool need = mx > m_ref + kRescaleThreshold;       // always true on the first block (m_ref = -inf)
+                float factor = 1.f;
+                if (need) { factor = ex2f(m_ref - mx); m_ref = mx; l *= factor; }
+                if (b >= 1) {
+                    // the previous block's P V must be in the accumulator before it may be rescaled
+                    mbar_wait(pv_done, (gb - 1) & 1);
+                    if (__any_sync(0xffffffffu, need)) {
+                        tc_fence_after_sync();
+                        uint32_t o0[32], o1[32];
+                        tmem_ld_32x32b_x32(lane_base + TM_O, o0);
+                        tmem_ld_32x32b_x32(lane_base + TM_O + 32, o1);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            o0[j] = __float_as_uint(__uint_as_float(o0[j]) * factor);
+                            o1[j] = __float_as_uint(__uint_as_float(o1[j]) * factor);
+                        }
+                        tmem_st_32x32b_x32(lane_base + TM_O, o0);
+                        tmem_st_32x32b_x32(lane_base + TM_O + 32, o1);
+                    }
+                }
+                const float nm = -m_ref;
+                float sum = 0.f;
+                uint32_t pk[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const float p0 = ex2f(fmaf(s[2 * j], p.scale_log2, nm));
+                    const float p1 = ex2f(fmaf(s[2 * j + 1], p.scale_log2, nm));
+                    sum += p0 + p1;
+                    pk[j] = pack_h2(p0, p1);
+                }
+                l += sum;
+                tmem_st_32x32b_x32(s_addr, pk);               // P over the first half of this S buffer
+                tmem_st_wait();
+                tc_fence_before_sync();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&p_ready[gb & 1]);
+            }
+            g += nb;
+            // ---- finalize: O / l, optional q8 fake-quant per 32-wide block, fp16 store of valid rows
+            mbar_wait(pv_done, (g - 1) & 1);
+            tc_fence_after_sync();
+            uint32_t o0[32], o1[32];
+            tmem_ld_32x32b_x32(lane_base + TM_O, o0);
+            tmem_ld_32x32b_x32(lane_base + TM_O + 32, o1);
+            tmem_ld_wait();
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(o_free);
+            const float inv = 1.f / l;
+            float v0[32], v1[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) { v0[j] = __uint_as_float(o0[j]) * inv; v1[j] = __uint_as_float(o1[j]) * inv; }
+            if (p.fq_type == W_Q4_0 || p.fq_type == W_Q4_1) { fake_quant32(v0, p.fq_type); fake_quant32(v1, p.fq_type); }
+            if (it.q0 + row < it.len) {
+                uint4 * op = reinterpret_cast<uint4 *>(p.out + (size_t) (it.t0 + it.q0 + row) * p.H + it.head * AD);
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    uint4 u;
+                    u.x = pack_h2(v0[8 * c], v0[8 * c + 1]); u.y = pack_h2(v0[8 * c + 2], v0[8 * c + 3]);
+                    u.z = pack_h2(v0[8 * c + 4], v0[8 * c + 5]); u.w = pack_h2(v0[8 * c + 6], v0[8 * c + 7]);
+                    op[c] = u;
+                }
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    uint4 u;
+                    u.x = pack_h2(v1[8 * c], v1[8 * c + 1]); u.y = pack_h2(v1[8 * c + 2], v1[8 * c + 3]);
+                    u.z = pack_h2(v1[8 * c + 4], v1[8 * c + 5]); u.w = pack_h2(v1[8 * c + 6], v1[8 * c + 7]);
+                    op[4 + c] = u;
+                }
+            }
+        }
+    }
+
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, TM_COLS);
+}
+
+}  // namespace
+
+bool make_attention_tmaps(CUtensorMap * tm_q, CUtensorMap * tm_kv, const __half * qkv, uint64_t rows, int H) {
+    return make_tmap_f16_2d(tm_q, qkv, rows, (uint64_t) 3 * H, AQ) && make_tmap_f16_2d(tm_kv, qkv, rows, (uint64_t) 3 * H, AK);
+}
+
+cudaError_t launch_attention_tc(const CUtensorMap * tm_q, const CUtensorMap * tm_kv, const int32_t * cu_seqlens,
+                                int n_sent, int max_len, int n_head, int d_head, __half * out, int fq_type,
+                                int num_sms, cudaStream_t st) {
+    if (n_sent <= 0) return cudaSuccess;
+    if (d_head != AD || !tm_q || !tm_kv) return cudaErrorInvalidValue;
+    cudaError_t e = cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmem);
+    if (e != cudaSuccess) return e;
+    AttnTcParams p;
+    p.cu = cu_seqlens; p.out = out; p.n_sent = n_sent; p.n_head = n_head; p.H = n_head * d_head;
+    p.max_qt = (max_len + AQ - 1) / AQ; p.fq_type = fq_type;
+    p.scale_log2 = 1.4426950408889634f / sqrtf((float) d_head);
+    const long long total = (long long) n_sent * n_head * p.max_qt;
+    if (total > 0x7fffffffLL) return cudaErrorInvalidValue;
+    const int grid = (int) (total < 2LL * num_sms ? total : 2LL * num_sms);
+    attention_tc_kernel<<<grid, ATT_TC_THREADS, kAttSmem, st>>>(*tm_q, *tm_kv, p);
+    return cudaGetLastError();
+}
+
+}  // namespace b200

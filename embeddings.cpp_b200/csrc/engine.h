@@ -47,6 +47,7 @@ struct Replica {
            * x1 = nullptr, * x1q = nullptr, * mid = nullptr;
     CUtensorMap tm_xin, tm_ctx, tm_x1in, tm_mid;     // A-operand maps (box 64 x 128)
     CUtensorMap to_qkv, to_y, to_mid;                // output maps (box 64 x 32, epilogue TMA stores)
+    CUtensorMap ta_q, ta_kv;                         // attention maps over qkv (box 64 x 128 / 64 x 64)
     CUtensorMap tr_x, tr_x1;                         // residual maps (box 64 x 32, epilogue TMA loads)
     static const int kSlots = 2;
     int32_t * d_ids[kSlots] = {nullptr, nullptr};    // [t_cap]
@@ -79,7 +80,7 @@ struct Engine {
     std::mutex mu;                             // a context is not re-entrant (bert.h note)
     std::atomic<int64_t> launches{0};
     int fq_type = -1;                          // W_Q4_0 / W_Q4_1 when activation fake-quant is on
-    bool gemm_simt = false, attn_ref = false;  // validation kernels forced by env (debug only)
+    bool gemm_simt = false, attn_ref = false, attn_mma = false;  // validation kernels forced by env (debug only)
     int t_cap = 0, b_cap = 0;
 
     ~Engine();

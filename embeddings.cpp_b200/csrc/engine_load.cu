@@ -182,10 +182,10 @@ bool Engine::init_devices(const ModelFile & mf) {
     if (devs.empty()) for (int i = 0; i < n_dev; ++i) devs.push_back(i);
 
     if (const char * e = getenv("BERT_GEMM_IMPL")) gemm_simt = strcmp(e, "simt") == 0;
-    if (const char * e = getenv("BERT_ATTN_IMPL")) attn_ref = strcmp(e, "ref") == 0;
+    if (const char * e = getenv("BERT_ATTN_IMPL")) { attn_ref = strcmp(e, "ref") == 0; attn_mma = strcmp(e, "mma") == 0; }
     fq_type = (hp.ftype == W_Q4_0 || hp.ftype == W_Q4_1) ? hp.ftype : -1;
     if (const char * e = getenv("BERT_ACT_QUANT")) { if (atoi(e) == 0) fq_type = -1; }
-    t_cap = 32768;
+    t_cap = 131072;
     if (const char * e = getenv("BERT_MICROBATCH_TOKENS")) { int v = atoi(e); if (v >= hp.n_max_tokens) t_cap = v; }
     if (t_cap < hp.n_max_tokens) t_cap = hp.n_max_tokens;
     b_cap = t_cap / 2 < 16384 ? t_cap / 2 : 16384;                // every sentence has >= 2 ids
@@ -326,6 +326,7 @@ bool Engine::alloc_workspace(Replica & r) {
     // deterministic contents for the never-written tail rows the GEMM tiles may read
     cudaMemsetAsync(r.x, 0, rows * H * 2, r.stream);
     if (fq) { cudaMemsetAsync(r.xq, 0, rows * H * 2, r.stream); cudaMemsetAsync(r.x1q, 0, rows * H * 2, r.stream); }
+    cudaMemsetAsync(r.qkv, 0, rows * 3 * H * 2, r.stream);       // attention may read (masked) rows past T: keep them finite
     cudaMemsetAsync(r.ctx, 0, rows * H * 2, r.stream);
     cudaMemsetAsync(r.x1, 0, rows * H * 2, r.stream);
     cudaMemsetAsync(r.mid, 0, rows * I * 2, r.stream);
@@ -333,6 +334,7 @@ bool Engine::alloc_workspace(Replica & r) {
         !make_tmap_f16_2d(&r.tm_x1in, r.x1q, rows, H, 128) || !make_tmap_f16_2d(&r.tm_mid, r.mid, rows, I, 128) ||
         !make_tmap_f16_2d(&r.to_qkv, r.qkv, rows, 3 * H, 32) || !make_tmap_f16_2d(&r.to_y, r.y, rows, H, 32) ||
         !make_tmap_f16_2d(&r.to_mid, r.mid, rows, I, 32) ||
+        !make_attention_tmaps(&r.ta_q, &r.ta_kv, r.qkv, rows, H) ||
         !make_tmap_f16_2d(&r.tr_x, r.x, rows, H, 32) || !make_tmap_f16_2d(&r.tr_x1, r.x1, rows, H, 32)) {
         fprintf(stderr, "bert_load_from_file: cuTensorMapEncodeTiled failed for an activation map\n");
         return false;

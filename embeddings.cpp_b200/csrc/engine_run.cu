@@ -60,8 +60,14 @@ bool Engine::forward(Replica & r, const int32_t * d_ids, const int32_t * d_cu, i
         const LayerDev & ly = r.layers[il];
         gemm(&r.tm_xin, &r.to_qkv, r.xq, ly.qkv, nullptr, nullptr, r.qkv, EPI_BIAS);
         begin(KK_ATTN);
-        L(KK_ATTN, (attn_ref ? launch_attention_ref : launch_attention)(r.qkv, d_cu, n_sent, max_len, hp.n_head,
-                                                                         H / hp.n_head, r.ctx, fq_type, st), "attention");
+        {
+            const int dh = H / hp.n_head;
+            cudaError_t ae;
+            if (attn_ref) ae = launch_attention_ref(r.qkv, d_cu, n_sent, max_len, hp.n_head, dh, r.ctx, fq_type, st);
+            else if (dh == 64 && !attn_mma) ae = launch_attention_tc(&r.ta_q, &r.ta_kv, d_cu, n_sent, max_len, hp.n_head, dh, r.ctx, fq_type, r.num_sms, st);
+            else ae = launch_attention(r.qkv, d_cu, n_sent, max_len, hp.n_head, dh, r.ctx, fq_type, st);
+            L(KK_ATTN, ae, "attention");
+        }
         end();
         gemm(&r.tm_ctx, &r.to_y, r.ctx, ly.o, r.x, &r.tr_x, r.y, EPI_BIAS | EPI_RESIDUAL);
         begin(KK_LN);

@@ -28,8 +28,9 @@ if step.startswith("gemm:"):
     rc, err, ref = pkg.selftest_gemm(int(M), int(N), int(K), int(wt), int(epi), 1)
     print(json.dumps({"step": step, "rc": rc, "max_err": err, "max_ref": ref}))
 elif step.startswith("attn:"):
-    _, ns, L, nh, d = step.split(":")
-    rc, err, ref = pkg.selftest_attention(int(ns), int(L), int(nh), int(d), 1)
+    f = step.split(":")                      # attn:n_sent:max_len:n_head:d_head[:seed]  (seed bit 1024: ramped keys, 2048: mma.sync kernel)
+    ns, L, nh, d = f[1:5]
+    rc, err, ref = pkg.selftest_attention(int(ns), int(L), int(nh), int(d), int(f[5]) if len(f) > 5 else 1)
     print(json.dumps({"step": step, "rc": rc, "max_err": err, "max_ref": ref}))
 elif step.startswith("parity:"):
     # parity:<shape>:<ftype>:<n_texts>:<max_len>
