@@ -23,19 +23,29 @@ constexpr int BK = 64;
 constexpr int UMMA_K = 16;
 constexpr int kSmemLimit = 232448;                   // 227 KB opt-in limit per CTA
 
-template <int BN> struct GemmCfg {
+template <int BN, int WT> struct GemmCfg {
+    static constexpr bool kQ4      = WT != W_F16;
     static constexpr int kBHalf    = BN / 2;                 // B rows this CTA supplies
     static constexpr int kABytes   = BM * BK * 2;
     static constexpr int kBBytes   = kBHalf * BK * 2;
-    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kNibBytes = BN * 16;                // 4-bit payload of one k-stage of this CTA's rows
+    static constexpr int kScaleBytes = BN * 2;               // fp16 d (and as much again for m)
+    static constexpr int kNibSlot  = kQ4 ? (kNibBytes + 2 * kScaleBytes + 127) / 128 * 128 : 0;
     static constexpr int kTmemCols = (2 * BN <= 128) ? 128 : (2 * BN <= 256 ? 256 : 512);
     static constexpr int kAccStride = BN <= 64 ? 64 : (BN <= 128 ? 128 : 256);
     static constexpr int kOutBytes = 4 * 2 * 4096;      // 4 epilogue warps x 2 buffers x [32 rows][128 B]
     static constexpr int kResBytes = 4 * 2 * 4096;      // same geometry, residual boxes prefetched by TMA
-    static constexpr int kFixed = kOutBytes + kResBytes + 1024 /*align slack*/ + 256 /*barriers*/;
-    static constexpr int kStagesFit = (kSmemLimit - kFixed) / kStageBytes;
-    static constexpr int kStages   = kStagesFit > 6 ? 6 : kStagesFit;
-    static constexpr int kSmemBytes = kStages * kStageBytes + kFixed;
+    static constexpr int kBarBytes = 512;
+    static constexpr int kFixed = kOutBytes + kResBytes + 1024 /*align slack*/ + kBarBytes;
+    // fp16 weights: A and B travel together through one ring.  q4 weights: A needs TMA-latency depth,
+    // the dequantised B only a short ring (it is produced from smem), the 4-bit ring hides L2 latency.
+    static constexpr int kFitF16   = (kSmemLimit - kFixed) / (kABytes + kBBytes);
+    static constexpr int kSA       = kQ4 ? 5 : (kFitF16 > 6 ? 6 : kFitF16);
+    static constexpr int kSB       = kQ4 ? 3 : kSA;
+    static constexpr int kSN       = kQ4 ? 6 : 0;
+    static constexpr int kSmemBytes = kSA * kABytes + kSB * kBBytes + kSN * kNibSlot + kFixed;
+    static_assert(kSmemBytes <= kSmemLimit, "shared memory budget");
+    static_assert(2 * kSA + 2 * kSB + 2 * kSN + 12 <= (kBarBytes - 8) / 8, "barrier region");
 };
 
 struct GemmParams {
@@ -122,27 +132,37 @@ struct TileWalk {
     __device__ __forceinline__ int tile(int i) const { return cid + i * ncl; }
 };
 
+constexpr int DQ_GROUPS = 2;                       // dequant warp groups; group g takes k-stages g, g + 2, ...
+constexpr int DQ_GROUP_WARPS = DQ_WARPS / DQ_GROUPS;
+template <int WT> constexpr int gemm_threads() { return WT == W_F16 ? 192 : 192 + 32 * DQ_WARPS + 32; }
+
 template <int BN, int WT>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(WT == W_F16 ? 192 : 192 + 32 * DQ_WARPS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(gemm_threads<WT>(), 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
                const GemmParams p) {
-    using Cfg = GemmCfg<BN>;
-    constexpr int S = Cfg::kStages;
+    using Cfg = GemmCfg<BN, WT>;
+    constexpr bool Q4 = Cfg::kQ4;
+    constexpr int SA = Cfg::kSA, SB = Cfg::kSB, SN = Cfg::kSN;
     constexpr int NB = BN / 64;                               // 64-column output boxes per tile
     extern __shared__ uint8_t smem_raw[];
     uint8_t * smem = (uint8_t *) (((uintptr_t) smem_raw + 1023) & ~(uintptr_t) 1023);
-    uint8_t * smem_a = smem;                                  // S x 16 KB
-    uint8_t * smem_b = smem + S * Cfg::kABytes;               // S x (BN/2)*128 B
-    uint8_t * smem_out = smem + S * Cfg::kStageBytes;         // 4 warps x 2 x 4 KB staging for TMA stores
+    uint8_t * smem_a = smem;                                  // SA x 16 KB
+    uint8_t * smem_b = smem_a + SA * Cfg::kABytes;            // SB x (BN/2)*128 B
+    uint8_t * smem_out = smem_b + SB * Cfg::kBBytes;          // 4 warps x 2 x 4 KB staging for TMA stores
     uint8_t * smem_res = smem_out + Cfg::kOutBytes;           // 4 warps x 2 x 4 KB residual boxes
-    uint64_t * bars = (uint64_t *) (smem_res + Cfg::kResBytes);
-    uint64_t * full = bars;                 // [S]   leader's copy is the live one
-    uint64_t * empty = bars + S;            // [S]   per CTA, signalled by the multicast commit
-    uint64_t * tfull = bars + 2 * S;        // [2]   per CTA, multicast commit
-    uint64_t * tempty = bars + 2 * S + 2;   // [2]   leader's copy is live: 8 epilogue warps arrive
-    uint64_t * rfull = bars + 2 * S + 4;    // [4][2] residual boxes, per epilogue warp
-    uint32_t * tmem_slot = (uint32_t *) (bars + 2 * S + 12);
+    uint8_t * smem_nib = smem_res + Cfg::kResBytes;           // SN x 4-bit weight stages (q4 only)
+    uint64_t * bars = (uint64_t *) (smem_nib + SN * Cfg::kNibSlot);
+    uint64_t * a_full = bars;                   // [SA]  leader's copy is live (A of both CTAs; + B for fp16 weights)
+    uint64_t * a_empty = a_full + SA;           // [SA]  per CTA, multicast commit
+    uint64_t * b_full = a_empty + SA;           // [SB]  q4: leader's copy, dequant warps of both CTAs arrive
+    uint64_t * b_empty = b_full + SB;           // [SB]  q4: per CTA, multicast commit
+    uint64_t * n_full = b_empty + SB;           // [SN]  q4: per CTA, bulk-copy bytes
+    uint64_t * n_empty = n_full + SN;           // [SN]  q4: per CTA, the dequant group that read the slot
+    uint64_t * tfull = n_empty + SN;            // [2]   per CTA, multicast commit
+    uint64_t * tempty = tfull + 2;              // [2]   leader's copy is live: 8 epilogue warps arrive
+    uint64_t * rfull = tempty + 2;              // [4][2] residual boxes, per epilogue warp
+    uint32_t * tmem_slot = (uint32_t *) (rfull + 8);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();                  // 0 = leader (issues the MMAs)
@@ -156,12 +176,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmap_a);
-        if (WT == W_F16) tma_prefetch_desc(&tmap_b);
+        if (!Q4) tma_prefetch_desc(&tmap_b);
         tma_prefetch_desc(&tmap_out);
         if (p.epilogue & EPI_RESIDUAL) tma_prefetch_desc(&tmap_res);
-        for (int s = 0; s < S; ++s) {
-            mbar_init(&full[s], WT == W_F16 ? 1 : 1 + 2 * DQ_WARPS);
-            mbar_init(&empty[s], 1);
+        for (int s = 0; s < SA; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
+        if (Q4) {
+            for (int s = 0; s < SB; ++s) { mbar_init(&b_full[s], 2 * DQ_GROUP_WARPS); mbar_init(&b_empty[s], 1); }
+            for (int s = 0; s < SN; ++s) { mbar_init(&n_full[s], 1); mbar_init(&n_empty[s], DQ_GROUP_WARPS); }
         }
         for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 8); }
         for (int i = 0; i < 8; ++i) mbar_init(&rfull[i], 1);
@@ -177,18 +198,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     if (warp == 0) {
         // ------------------------------------------------------------ TMA producer (both CTAs)
         if (lane == 0) {
-            const uint32_t full_leader = mapa_u32(smem_u32(&full[0]), 0);
+            const uint32_t full_leader = mapa_u32(smem_u32(&a_full[0]), 0);
             int s = 0; uint32_t ph = 0;
             for (int i = 0; i < my_tiles; ++i) {
                 const int tile = tw.tile(i);
                 const int m0 = (tile / tw.num_n) * (2 * BM) + (int) rank * BM;
                 const int nb0 = (tile % tw.num_n) * BN + (int) rank * Cfg::kBHalf;
                 for (int kb = 0; kb < num_k; ++kb) {
-                    mbar_wait(&empty[s], ph ^ 1);
-                    if (rank == 0) mbar_expect_tx(&full[s], 2 * (WT == W_F16 ? Cfg::kStageBytes : Cfg::kABytes));
+                    mbar_wait(&a_empty[s], ph ^ 1);
+                    if (rank == 0) mbar_expect_tx(&a_full[s], 2 * (Q4 ? Cfg::kABytes : Cfg::kABytes + Cfg::kBBytes));
                     tma_load_2d_pair(smem_a + s * Cfg::kABytes, &tmap_a, full_leader + 8 * s, kb * BK, m0);
-                    if (WT == W_F16) tma_load_2d_pair(smem_b + s * Cfg::kBBytes, &tmap_b, full_leader + 8 * s, kb * BK, nb0);
-                    if (++s == S) { s = 0; ph ^= 1; }
+                    if (!Q4) tma_load_2d_pair(smem_b + s * Cfg::kBBytes, &tmap_b, full_leader + 8 * s, kb * BK, nb0);
+                    if (++s == SA) { s = 0; ph ^= 1; }
                 }
             }
         }
@@ -196,7 +217,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         // ------------------------------------------------------------ MMA issuer (leader CTA only)
         if (rank == 0) {
             constexpr uint32_t idesc = umma_idesc_f16(2 * BM, BN);
-            int s = 0; uint32_t ph = 0;
+            int sa = 0, sb = 0; uint32_t pha = 0, phb = 0;
             for (int it = 0; it < my_tiles; ++it) {
                 const int acc = it & 1;
                 const uint32_t acc_ph = (it >> 1) & 1;
@@ -204,21 +225,24 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 tc_fence_after_sync();
                 const uint32_t d_tmem = tmem_base + acc * Cfg::kAccStride;
                 for (int kb = 0; kb < num_k; ++kb) {
-                    mbar_wait(&full[s], ph);
+                    mbar_wait(&a_full[sa], pha);
+                    if (Q4) mbar_wait(&b_full[sb], phb);
                     tc_fence_after_sync();
                     if (elect_one()) {
-                        const uint64_t adesc = umma_smem_desc_sw128(smem_u32(smem_a + s * Cfg::kABytes));
-                        const uint64_t bdesc = umma_smem_desc_sw128(smem_u32(smem_b + s * Cfg::kBBytes));
+                        const uint64_t adesc = umma_smem_desc_sw128(smem_u32(smem_a + sa * Cfg::kABytes));
+                        const uint64_t bdesc = umma_smem_desc_sw128(smem_u32(smem_b + sb * Cfg::kBBytes));
 #pragma unroll
                         for (int k = 0; k < BK / UMMA_K; ++k) {
                             // +32 B per K=16 step inside the 128-B swizzle row (address field is >>4)
                             umma_f16_ss_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
                         }
-                        umma_commit_pair(&empty[s]);                          // frees the stage in both CTAs
+                        umma_commit_pair(&a_empty[sa]);                       // frees the stage in both CTAs
+                        if (Q4) umma_commit_pair(&b_empty[sb]);
                         if (kb == num_k - 1) umma_commit_pair(&tfull[acc]);   // accumulators ready in both CTAs
                     }
                     __syncwarp();
-                    if (++s == S) { s = 0; ph ^= 1; }
+                    if (++sa == SA) { sa = 0; pha ^= 1; }
+                    if (++sb == SB) { sb = 0; phb ^= 1; }
                 }
             }
         }
@@ -320,50 +344,45 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             if (lane == 0) mbar_arrive_cluster(tempty_leader + 8 * acc);
         }
         if (lane == 0) tma_store_wait_all<0>();
-    } else {
-        // ------------------------------------------------------------ q4 dequant producers (both CTAs)
-        // Each CTA dequantises the BN/2 weight rows it contributes to the pair's B operand.  The
-        // 4-bit loads run two k-stages ahead of the stage being written (register ring), so the
-        // L2 latency is off the critical path.
-        if (WT != W_F16) {
-            constexpr int DQT = 32 * DQ_WARPS;
+    } else if (warp < 6 + DQ_WARPS) {
+        // ------------------------------------------------------------ q4 dequant (both CTAs)
+        // Each CTA dequantises the BN/2 weight rows it contributes to the pair's B operand, reading
+        // the 4-bit stage from the smem ring the bulk-copy warp fills (no global loads here, so the
+        // proxy fence never waits on HBM/L2).  Two warp groups take alternate k-stages.
+        if constexpr (Q4) {
+            constexpr int GT = 32 * DQ_GROUP_WARPS;              // threads per group
             constexpr int NUNIT = BN;                            // 32-weight blocks per CTA per stage
-            constexpr int UNITS = (NUNIT + DQT - 1) / DQT;       // per thread
-            const int t = threadIdx.x - 192;                     // 0..DQT-1
-            const uint32_t full_leader = mapa_u32(smem_u32(&full[0]), 0);
-            struct Regs { uint4 nib[UNITS]; __half d[UNITS], m[UNITS]; };
+            constexpr int UNITS = (NUNIT + GT - 1) / GT;         // per thread
+            const int grp = (warp - 6) / DQ_GROUP_WARPS;
+            const int tg = threadIdx.x - 192 - grp * GT;         // 0..GT-1
+            const uint32_t bfull_leader = mapa_u32(smem_u32(&b_full[0]), 0);
             const int total = my_tiles * num_k;
-            int ld_i = 0, ld_kb = 0, ld_it = 0;                  // load cursor: iteration, its k-stage, its tile slot
-            auto load = [&](Regs & R) {
-                if (ld_i < total) {
-                    const int tile = tw.tile(ld_it);
-                    const int nb0 = (tile % tw.num_n) * BN + (int) rank * Cfg::kBHalf;
-                    // stage kb of rows nb0..nb0+BN/2-1 is contiguous: [kb][n][2] blocks
-                    const size_t blk0 = ((size_t) ld_kb * p.N + nb0) * 2;
-#pragma unroll
-                    for (int u = 0; u < UNITS; ++u) {
-                        if (t + DQT * u < NUNIT) {
-                            const size_t b = blk0 + t + DQT * u;
-                            R.nib[u] = __ldg(p.qnib + b);
-                            R.d[u] = __ldg(p.qd + b);
-                            R.m[u] = WT == W_Q4_1 ? __ldg(p.qm + b) : __half();
-                        }
-                    }
-                    ++ld_i;
-                    if (++ld_kb == num_k) { ld_kb = 0; ++ld_it; }
-                }
-            };
-            int s = 0; uint32_t ph = 0;
-            auto emit = [&](const Regs & R) {
-                mbar_wait(&empty[s], ph ^ 1);
-                uint8_t * bt = smem_b + s * Cfg::kBBytes;
+            int sn = grp % SN, sb = grp % SB;
+            uint32_t phn = 0, phb = 0;
+            for (int i = grp; i < total; i += DQ_GROUPS) {
+                const uint8_t * slot = smem_nib + sn * Cfg::kNibSlot;
+                mbar_wait(&n_full[sn], phn);
+                uint4 nib[UNITS]; __half d[UNITS], m[UNITS];
 #pragma unroll
                 for (int u = 0; u < UNITS; ++u) {
-                    const int unit = t + DQT * u;
+                    const int unit = tg + GT * u;
+                    if (unit < NUNIT) {
+                        nib[u] = *reinterpret_cast<const uint4 *>(slot + unit * 16);
+                        d[u] = *reinterpret_cast<const __half *>(slot + Cfg::kNibBytes + unit * 2);
+                        m[u] = WT == W_Q4_1 ? *reinterpret_cast<const __half *>(slot + Cfg::kNibBytes + Cfg::kScaleBytes + unit * 2) : __half();
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&n_empty[sn]);            // slot may be refilled
+                mbar_wait(&b_empty[sb], phb ^ 1);
+                uint8_t * bt = smem_b + sb * Cfg::kBBytes;
+#pragma unroll
+                for (int u = 0; u < UNITS; ++u) {
+                    const int unit = tg + GT * u;
                     if (unit >= NUNIT) continue;
                     const int r = unit >> 1, half_k = unit & 1;          // row in this CTA's half, which 32-block
-                    const __half2 d2 = __half2half2(R.d[u]), m2 = __half2half2(R.m[u]);
-                    const uint32_t w[4] = {R.nib[u].x, R.nib[u].y, R.nib[u].z, R.nib[u].w};
+                    const __half2 d2 = __half2half2(d[u]), m2 = __half2half2(m[u]);
+                    const uint32_t w[4] = {nib[u].x, nib[u].y, nib[u].z, nib[u].w};
 #pragma unroll
                     for (int c = 0; c < 4; ++c) {
                         uint4 o;
@@ -377,18 +396,30 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 }
                 fence_proxy_async_smem();
                 __syncwarp();
-                if (lane == 0) mbar_arrive_cluster(full_leader + 8 * s);
-                if (++s == S) { s = 0; ph ^= 1; }
-            };
-            Regs r0, r1;
-            load(r0);
-            load(r1);
-            for (int i = 0; i < total; i += 2) {
-                emit(r0);
-                load(r0);
-                if (i + 1 < total) {
-                    emit(r1);
-                    load(r1);
+                if (lane == 0) mbar_arrive_cluster(bfull_leader + 8 * sb);
+                sn += DQ_GROUPS; if (sn >= SN) { sn -= SN; phn ^= 1; }
+                sb += DQ_GROUPS; if (sb >= SB) { sb -= SB; phb ^= 1; }
+            }
+        }
+    } else {
+        // ------------------------------------------------------------ 4-bit weight stream (both CTAs)
+        // One thread bulk-copies each k-stage of this CTA's rows (nibbles | d | m planes, each
+        // contiguous in HBM) into the smem ring, SN stages ahead of the dequant warps.
+        if constexpr (Q4) if (lane == 0) {
+            int s = 0; uint32_t ph = 0;
+            constexpr uint32_t kBytes = Cfg::kNibBytes + (WT == W_Q4_1 ? 2 : 1) * Cfg::kScaleBytes;
+            for (int i = 0; i < my_tiles; ++i) {
+                const int tile = tw.tile(i);
+                const int nb0 = (tile % tw.num_n) * BN + (int) rank * Cfg::kBHalf;
+                for (int kb = 0; kb < num_k; ++kb) {
+                    const size_t blk0 = ((size_t) kb * p.N + nb0) * 2;      // stage kb of rows nb0.. : [kb][n][2] blocks
+                    uint8_t * slot = smem_nib + s * Cfg::kNibSlot;
+                    mbar_wait(&n_empty[s], ph ^ 1);
+                    mbar_expect_tx(&n_full[s], kBytes);
+                    bulk_load_1d(slot, p.qnib + blk0, Cfg::kNibBytes, &n_full[s]);
+                    bulk_load_1d(slot + Cfg::kNibBytes, p.qd + blk0, Cfg::kScaleBytes, &n_full[s]);
+                    if (WT == W_Q4_1) bulk_load_1d(slot + Cfg::kNibBytes + Cfg::kScaleBytes, p.qm + blk0, Cfg::kScaleBytes, &n_full[s]);
+                    if (++s == SN) { s = 0; ph ^= 1; }
                 }
             }
         }
@@ -405,10 +436,10 @@ template <int BN, int WT>
 static int max_clusters(int device, int num_sms) {
     static int cached[64] = {0};
     if (device >= 0 && device < 64 && cached[device] > 0) return cached[device];
-    using Cfg = GemmCfg<BN>;
+    using Cfg = GemmCfg<BN, WT>;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned) (num_sms & ~1));
-    cfg.blockDim = dim3(WT == W_F16 ? 192 : 192 + 32 * DQ_WARPS);
+    cfg.blockDim = dim3(gemm_threads<WT>());
     cfg.dynamicSmemBytes = Cfg::kSmemBytes;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
@@ -426,8 +457,8 @@ static int max_clusters(int device, int num_sms) {
 
 template <int BN, int WT>
 static cudaError_t launch_one(const GemmArgs & g, int num_sms, cudaStream_t st) {
-    using Cfg = GemmCfg<BN>;
-    static_assert(Cfg::kStages >= 3, "pipeline too shallow");
+    using Cfg = GemmCfg<BN, WT>;
+    static_assert(Cfg::kSA >= 3, "pipeline too shallow");
     auto kern = gemm_tc_kernel<BN, WT>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
     if (e != cudaSuccess) return e;
@@ -441,7 +472,7 @@ static cudaError_t launch_one(const GemmArgs & g, int num_sms, cudaStream_t st) 
     if (ncl <= 0) return cudaSuccess;
     if ((g.epilogue & EPI_RESIDUAL) && !g.tmap_res) return cudaErrorInvalidValue;
     const CUtensorMap * tres = g.tmap_res ? g.tmap_res : g.tmap_out;
-    kern<<<2 * ncl, WT == W_F16 ? 192 : 192 + 32 * DQ_WARPS, Cfg::kSmemBytes, st>>>(*g.tmap_a, w.tmap, *g.tmap_out, *tres, p);
+    kern<<<2 * ncl, gemm_threads<WT>(), Cfg::kSmemBytes, st>>>(*g.tmap_a, w.tmap, *g.tmap_out, *tres, p);
     return cudaGetLastError();
 }
 

@@ -72,6 +72,13 @@ __device__ __forceinline__ void tma_load_2d(void * smem_dst, const void * tmap, 
         : "memory");
 }
 
+// 1-D bulk copy global -> this CTA's smem, bytes signalled on a local mbarrier (16-B aligned, size % 16 == 0)
+__device__ __forceinline__ void bulk_load_1d(void * smem_dst, const void * gsrc, uint32_t bytes, uint64_t * bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+        :: "r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
 // ---------------------------------------------------------------- tcgen05 / TMEM
 __device__ __forceinline__ void tmem_alloc(uint32_t * smem_result, uint32_t ncols) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
