@@ -33,10 +33,11 @@ template <int BN, int WT> struct GemmCfg {
     static constexpr int kNibSlot  = kQ4 ? (kNibBytes + 2 * kScaleBytes + 127) / 128 * 128 : 0;
     static constexpr int kTmemCols = (2 * BN <= 128) ? 128 : (2 * BN <= 256 ? 256 : 512);
     static constexpr int kAccStride = BN <= 64 ? 64 : (BN <= 128 ? 128 : 256);
-    static constexpr int kOutBytes = 4 * 2 * 4096;      // 4 epilogue warps x 2 buffers x [32 rows][128 B]
-    static constexpr int kResBytes = 4 * 2 * 4096;      // same geometry, residual boxes prefetched by TMA
+    static constexpr int kOutBytes = 8 * 4096;          // 8 epilogue warps x [32 rows][128 B] staging for TMA stores
+    static constexpr int kResBytes = 8 * 4096;          // same geometry, residual boxes prefetched by TMA
+    static constexpr int kBiasBytes = 8 * 256;          // per warp: the 64 bias values of its current box
     static constexpr int kBarBytes = 512;
-    static constexpr int kFixed = kOutBytes + kResBytes + 1024 /*align slack*/ + kBarBytes;
+    static constexpr int kFixed = kOutBytes + kResBytes + kBiasBytes + 1024 /*align slack*/ + kBarBytes;
     // fp16 weights: A and B travel together through one ring.  q4 weights: A needs TMA-latency depth,
     // the dequantised B only a short ring (it is produced from smem), the 4-bit ring hides L2 latency.
     static constexpr int kFitF16   = (kSmemLimit - kFixed) / (kABytes + kBBytes);
@@ -106,6 +107,7 @@ template <int N> __device__ __forceinline__ void tma_store_wait_all() {
 }
 
 constexpr int DQ_WARPS = 8;          // q4 dequant producer warps (two per SM sub-partition)
+constexpr int EPI_WARPS = 8;         // epilogue warps (two per TMEM lane quadrant)
 
 // two nibbles -> two fp16 weights.  `w` holds e(2i) at bits [4i,4i+4), e(2i+1) at [16+4i,..).
 // The nibble is OR-ed into the mantissa of an fp16 constant whose ulp matches the nibble's
@@ -134,7 +136,13 @@ struct TileWalk {
 
 constexpr int DQ_GROUPS = 2;                       // dequant warp groups; group g takes k-stages g, g + 2, ...
 constexpr int DQ_GROUP_WARPS = DQ_WARPS / DQ_GROUPS;
-template <int WT> constexpr int gemm_threads() { return WT == W_F16 ? 192 : 192 + 32 * DQ_WARPS + 32; }
+// Warp roles, aligned to warpgroups so that registers can be re-balanced with setmaxnreg:
+//   warps 0-3   control: 0 TMA producer, 1 MMA issuer, 2 4-bit weight stream (q4), 3 idle
+//   warps 4-11  epilogue (two warpgroups)
+//   warps 12-19 q4 dequant (two warpgroups; absent for fp16 weights)
+constexpr int CTRL_WARPS = 4;
+template <int WT> constexpr int gemm_threads() { return 32 * (CTRL_WARPS + EPI_WARPS + (WT == W_F16 ? 0 : DQ_WARPS)); }
+constexpr int kRegsCtrl = 40, kRegsDequant = 56, kRegsEpilogue = 160;     // q4: 640 threads launch with 96
 
 template <int BN, int WT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(gemm_threads<WT>(), 1)
@@ -149,9 +157,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     uint8_t * smem = (uint8_t *) (((uintptr_t) smem_raw + 1023) & ~(uintptr_t) 1023);
     uint8_t * smem_a = smem;                                  // SA x 16 KB
     uint8_t * smem_b = smem_a + SA * Cfg::kABytes;            // SB x (BN/2)*128 B
-    uint8_t * smem_out = smem_b + SB * Cfg::kBBytes;          // 4 warps x 2 x 4 KB staging for TMA stores
-    uint8_t * smem_res = smem_out + Cfg::kOutBytes;           // 4 warps x 2 x 4 KB residual boxes
-    uint8_t * smem_nib = smem_res + Cfg::kResBytes;           // SN x 4-bit weight stages (q4 only)
+    uint8_t * smem_out = smem_b + SB * Cfg::kBBytes;          // 8 warps x 4 KB staging for TMA stores
+    uint8_t * smem_res = smem_out + Cfg::kOutBytes;           // 8 warps x 4 KB residual boxes
+    uint8_t * smem_bias = smem_res + Cfg::kResBytes;          // 8 warps x 64 floats
+    uint8_t * smem_nib = smem_bias + Cfg::kBiasBytes;         // SN x 4-bit weight stages (q4 only)
     uint64_t * bars = (uint64_t *) (smem_nib + SN * Cfg::kNibSlot);
     uint64_t * a_full = bars;                   // [SA]  leader's copy is live (A of both CTAs; + B for fp16 weights)
     uint64_t * a_empty = a_full + SA;           // [SA]  per CTA, multicast commit
@@ -160,8 +169,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     uint64_t * n_full = b_empty + SB;           // [SN]  q4: per CTA, bulk-copy bytes
     uint64_t * n_empty = n_full + SN;           // [SN]  q4: per CTA, the dequant group that read the slot
     uint64_t * tfull = n_empty + SN;            // [2]   per CTA, multicast commit
-    uint64_t * tempty = tfull + 2;              // [2]   leader's copy is live: 8 epilogue warps arrive
-    uint64_t * rfull = tempty + 2;              // [4][2] residual boxes, per epilogue warp
+    uint64_t * tempty = tfull + 2;              // [2]   leader's copy is live: 16 epilogue warps arrive
+    uint64_t * rfull = tempty + 2;              // [8] residual box, per epilogue warp
     uint32_t * tmem_slot = (uint32_t *) (rfull + 8);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -184,7 +193,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             for (int s = 0; s < SB; ++s) { mbar_init(&b_full[s], 2 * DQ_GROUP_WARPS); mbar_init(&b_empty[s], 1); }
             for (int s = 0; s < SN; ++s) { mbar_init(&n_full[s], 1); mbar_init(&n_empty[s], DQ_GROUP_WARPS); }
         }
-        for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 8); }
+        for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 2 * EPI_WARPS); }
         for (int i = 0; i < 8; ++i) mbar_init(&rfull[i], 1);
         fence_mbar_init();
     }
@@ -195,7 +204,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp == 0) {
+    if (warp < CTRL_WARPS) {
+      if constexpr (Q4) reg_dealloc<kRegsCtrl>();
+      if (warp == 0) {
         // ------------------------------------------------------------ TMA producer (both CTAs)
         if (lane == 0) {
             const uint32_t full_leader = mapa_u32(smem_u32(&a_full[0]), 0);
@@ -213,7 +224,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 }
             }
         }
-    } else if (warp == 1) {
+      } else if (warp == 1) {
         // ------------------------------------------------------------ MMA issuer (leader CTA only)
         if (rank == 0) {
             constexpr uint32_t idesc = umma_idesc_f16(2 * BM, BN);
@@ -246,28 +257,65 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 }
             }
         }
-    } else if (warp < 6) {
-        // ------------------------------------------------------------ epilogue (4 warps per CTA)
-        // Per 64-column box: TMEM -> registers ; bias / GELU / + residual (own row of the box the
+      } else if (warp == 2) {
+        // ------------------------------------------------------------ 4-bit weight stream (both CTAs)
+        // One thread bulk-copies each k-stage of this CTA's rows (nibbles | d | m planes, each
+        // contiguous in HBM) into the smem ring, SN stages ahead of the dequant warps.
+        if constexpr (Q4) if (lane == 0) {
+            int s = 0; uint32_t ph = 0;
+            constexpr uint32_t kBytes = Cfg::kNibBytes + (WT == W_Q4_1 ? 2 : 1) * Cfg::kScaleBytes;
+            for (int i = 0; i < my_tiles; ++i) {
+                const int tile = tw.tile(i);
+                const int nb0 = (tile % tw.num_n) * BN + (int) rank * Cfg::kBHalf;
+                for (int kb = 0; kb < num_k; ++kb) {
+                    const size_t blk0 = ((size_t) kb * p.N + nb0) * 2;      // stage kb of rows nb0.. : [kb][n][2] blocks
+                    uint8_t * slot = smem_nib + s * Cfg::kNibSlot;
+                    mbar_wait(&n_empty[s], ph ^ 1);
+                    mbar_expect_tx(&n_full[s], kBytes);
+                    bulk_load_1d(slot, p.qnib + blk0, Cfg::kNibBytes, &n_full[s]);
+                    bulk_load_1d(slot + Cfg::kNibBytes, p.qd + blk0, Cfg::kScaleBytes, &n_full[s]);
+                    if (WT == W_Q4_1) bulk_load_1d(slot + Cfg::kNibBytes + Cfg::kScaleBytes, p.qm + blk0, Cfg::kScaleBytes, &n_full[s]);
+                    if (++s == SN) { s = 0; ph ^= 1; }
+                }
+            }
+        }
+      }
+    } else if (warp < CTRL_WARPS + EPI_WARPS) {
+      if constexpr (Q4) reg_alloc<kRegsEpilogue>();
+        // ------------------------------------------------------------ epilogue (8 warps per CTA)
+        // Two warps per TMEM lane quadrant take alternate 64-column boxes of the tile, so every
+        // scheduler has two epilogue warps to interleave.  Per box: TMEM -> registers ; bias (from a
+        // warp-private smem slot filled one box ahead) / GELU / + residual (own row of the box the
         // warp prefetched by TMA) / q8 fake-quant ; fp16 -> swizzled smem ; one TMA store of the
         // warp's [32 rows x 64 cols] sub-box.  Global traffic is whole 128-B rows in both
         // directions; everything is warp-local (no CTA barrier).
+        const int e = warp - CTRL_WARPS;           // 0..7
         const int q = warp & 3;                    // TMEM lane quadrant this warp may access
-        uint8_t * out_base = smem_out + (warp - 2) * 2 * 4096;
-        uint8_t * res_base = smem_res + (warp - 2) * 2 * 4096;
-        uint64_t * rbar = rfull + (warp - 2) * 2;
+        const int half = e >> 2;                   // which of the quadrant's two warps
+        constexpr int NBW0 = (NB + 1) / 2, NBW1 = NB / 2;
+        const int nbw = half == 0 ? NBW0 : NBW1;   // boxes of a tile this warp owns: half, half + 2, ...
+        uint8_t * st = smem_out + e * 4096;
+        uint8_t * rs = smem_res + e * 4096;
+        float * bslot = reinterpret_cast<float *>(smem_bias + e * 256);
+        uint64_t * rbar = rfull + e;
         const uint32_t tempty_leader = mapa_u32(smem_u32(&tempty[0]), 0);
         const bool has_res = (p.epilogue & EPI_RESIDUAL) != 0;
-        const int total_boxes = my_tiles * NB;
-        auto box_coords = [&](int j, int & c0, int & row0) {
-            const int tile = tw.tile(j / NB);
-            c0 = (tile % tw.num_n) * BN + (j % NB) * 64;
+        const bool has_bias = (p.epilogue & EPI_BIAS) != 0;
+        const int total_boxes = my_tiles * nbw;
+        auto box_coords = [&](int j, int & c0, int & row0, int & b) {
+            const int tile = tw.tile(j / nbw);
+            b = half + 2 * (j % nbw);
+            c0 = (tile % tw.num_n) * BN + b * 64;
             row0 = (tile / tw.num_n) * (2 * BM) + (int) rank * BM + q * 32;
         };
-        if (has_res && lane == 0 && total_boxes > 0) {
-            int c0, row0; box_coords(0, c0, row0);
-            mbar_expect_tx(&rbar[0], 4096);
-            tma_load_2d(res_base, &tmap_res, &rbar[0], c0, row0);
+        float2 bnext = make_float2(0.f, 0.f);
+        if (total_boxes > 0) {
+            int c0, row0, b; box_coords(0, c0, row0, b);
+            if (has_res && lane == 0) {
+                mbar_expect_tx(rbar, 4096);
+                tma_load_2d(rs, &tmap_res, rbar, c0, row0);
+            }
+            if (has_bias) bnext = __ldg(reinterpret_cast<const float2 *>(p.bias + c0) + lane);
         }
         int j = 0;
         for (int it = 0; it < my_tiles; ++it) {
@@ -276,21 +324,27 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             mbar_wait(&tfull[acc], acc_ph);
             tc_fence_after_sync();
 #pragma unroll 1
-            for (int b = 0; b < NB; ++b, ++j) {
-                uint8_t * st = out_base + (j & 1) * 4096;
-                const uint8_t * rs = res_base + (j & 1) * 4096;
-                int c0, wrow0; box_coords(j, c0, wrow0);
-                // the TMA store that last read this buffer (two boxes ago) must be done reading
-                if (lane == 0) tma_store_wait_read<1>();
+            for (int bi = 0; bi < nbw; ++bi, ++j) {
+                int c0, wrow0, b; box_coords(j, c0, wrow0, b);
+                // this box's bias -> smem slot (read back as broadcast LDS.128); next box's bias -> registers
+                reinterpret_cast<float2 *>(bslot)[lane] = bnext;
+                uint4 rr[8];
                 if (has_res) {
-                    if (lane == 0 && j + 1 < total_boxes) {       // prefetch the next box's residual
-                        int c1, r1; box_coords(j + 1, c1, r1);
-                        mbar_expect_tx(&rbar[(j + 1) & 1], 4096);
-                        tma_load_2d(res_base + ((j + 1) & 1) * 4096, &tmap_res, &rbar[(j + 1) & 1], c1, r1);
-                    }
-                    mbar_wait(&rbar[j & 1], (j >> 1) & 1);
+                    mbar_wait(rbar, j & 1);
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) rr[c] = *reinterpret_cast<const uint4 *>(rs + lane * 128 + ((c ^ (lane & 7)) << 4));
+                    // force the last shared load to have landed before the buffer is handed back to the TMA
+                    uint32_t sink; asm volatile("mov.b32 %0, %1;" : "=r"(sink) : "r"(rr[7].w));
                 }
                 __syncwarp();
+                if (j + 1 < total_boxes) {
+                    int c1, r1, b1; box_coords(j + 1, c1, r1, b1);
+                    if (has_res && lane == 0) {                   // prefetch the next box's residual
+                        mbar_expect_tx(rbar, 4096);
+                        tma_load_2d(rs, &tmap_res, rbar, c1, r1);
+                    }
+                    if (has_bias) bnext = __ldg(reinterpret_cast<const float2 *>(p.bias + c1) + lane);
+                }
 #pragma unroll
                 for (int hh = 0; hh < 2; ++hh) {
                     uint32_t r[32];
@@ -299,10 +353,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     float2 v[16];
 #pragma unroll
                     for (int i = 0; i < 16; ++i) v[i] = make_float2(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1]));
-                    if (p.epilogue & EPI_BIAS) {
+                    if (has_bias) {
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
-                            const float4 bb = __ldg(reinterpret_cast<const float4 *>(p.bias + c0 + hh * 32) + i);
+                            const float4 bb = *reinterpret_cast<const float4 *>(bslot + hh * 32 + 4 * i);
                             v[2 * i] = __fadd2_rn(v[2 * i], make_float2(bb.x, bb.y));
                             v[2 * i + 1] = __fadd2_rn(v[2 * i + 1], make_float2(bb.z, bb.w));
                         }
@@ -314,21 +368,24 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     if (has_res) {
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
-                            const int c = hh * 4 + i;
-                            const uint4 u = *reinterpret_cast<const uint4 *>(rs + lane * 128 + ((c ^ (lane & 7)) << 4));
-                            const __half2 * h = reinterpret_cast<const __half2 *>(&u);
+                            const __half2 * h = reinterpret_cast<const __half2 *>(&rr[hh * 4 + i]);
 #pragma unroll
-                            for (int e = 0; e < 4; ++e) v[i * 4 + e] = __fadd2_rn(v[i * 4 + e], __half22float2(h[e]));
+                            for (int k = 0; k < 4; ++k) v[i * 4 + k] = __fadd2_rn(v[i * 4 + k], __half22float2(h[k]));
                         }
                     }
                     if (p.epilogue & EPI_FAKEQUANT) fake_quant32_v2(v, p.fq_type);
+                    if (hh == 0) {
+                        // the TMA store of this warp's previous box must be done reading the staging buffer
+                        if (lane == 0) tma_store_wait_read<0>();
+                        __syncwarp();
+                    }
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
                         const int c = hh * 4 + i;
                         uint4 u;
                         __half2 * h = reinterpret_cast<__half2 *>(&u);
 #pragma unroll
-                        for (int e = 0; e < 4; ++e) h[e] = __floats2half2_rn(v[i * 4 + e].x, v[i * 4 + e].y);
+                        for (int k = 0; k < 4; ++k) h[k] = __floats2half2_rn(v[i * 4 + k].x, v[i * 4 + k].y);
                         *reinterpret_cast<uint4 *>(st + lane * 128 + ((c ^ (lane & 7)) << 4)) = u;
                     }
                 }
@@ -344,7 +401,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             if (lane == 0) mbar_arrive_cluster(tempty_leader + 8 * acc);
         }
         if (lane == 0) tma_store_wait_all<0>();
-    } else if (warp < 6 + DQ_WARPS) {
+    } else {
+      if constexpr (Q4) reg_dealloc<kRegsDequant>();
         // ------------------------------------------------------------ q4 dequant (both CTAs)
         // Each CTA dequantises the BN/2 weight rows it contributes to the pair's B operand, reading
         // the 4-bit stage from the smem ring the bulk-copy warp fills (no global loads here, so the
@@ -353,8 +411,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             constexpr int GT = 32 * DQ_GROUP_WARPS;              // threads per group
             constexpr int NUNIT = BN;                            // 32-weight blocks per CTA per stage
             constexpr int UNITS = (NUNIT + GT - 1) / GT;         // per thread
-            const int grp = (warp - 6) / DQ_GROUP_WARPS;
-            const int tg = threadIdx.x - 192 - grp * GT;         // 0..GT-1
+            const int grp = (warp - CTRL_WARPS - EPI_WARPS) / DQ_GROUP_WARPS;
+            const int tg = threadIdx.x - 32 * (CTRL_WARPS + EPI_WARPS) - grp * GT;         // 0..GT-1
             const uint32_t bfull_leader = mapa_u32(smem_u32(&b_full[0]), 0);
             const int total = my_tiles * num_k;
             int sn = grp % SN, sb = grp % SB;
@@ -399,28 +457,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 if (lane == 0) mbar_arrive_cluster(bfull_leader + 8 * sb);
                 sn += DQ_GROUPS; if (sn >= SN) { sn -= SN; phn ^= 1; }
                 sb += DQ_GROUPS; if (sb >= SB) { sb -= SB; phb ^= 1; }
-            }
-        }
-    } else {
-        // ------------------------------------------------------------ 4-bit weight stream (both CTAs)
-        // One thread bulk-copies each k-stage of this CTA's rows (nibbles | d | m planes, each
-        // contiguous in HBM) into the smem ring, SN stages ahead of the dequant warps.
-        if constexpr (Q4) if (lane == 0) {
-            int s = 0; uint32_t ph = 0;
-            constexpr uint32_t kBytes = Cfg::kNibBytes + (WT == W_Q4_1 ? 2 : 1) * Cfg::kScaleBytes;
-            for (int i = 0; i < my_tiles; ++i) {
-                const int tile = tw.tile(i);
-                const int nb0 = (tile % tw.num_n) * BN + (int) rank * Cfg::kBHalf;
-                for (int kb = 0; kb < num_k; ++kb) {
-                    const size_t blk0 = ((size_t) kb * p.N + nb0) * 2;      // stage kb of rows nb0.. : [kb][n][2] blocks
-                    uint8_t * slot = smem_nib + s * Cfg::kNibSlot;
-                    mbar_wait(&n_empty[s], ph ^ 1);
-                    mbar_expect_tx(&n_full[s], kBytes);
-                    bulk_load_1d(slot, p.qnib + blk0, Cfg::kNibBytes, &n_full[s]);
-                    bulk_load_1d(slot + Cfg::kNibBytes, p.qd + blk0, Cfg::kScaleBytes, &n_full[s]);
-                    if (WT == W_Q4_1) bulk_load_1d(slot + Cfg::kNibBytes + Cfg::kScaleBytes, p.qm + blk0, Cfg::kScaleBytes, &n_full[s]);
-                    if (++s == SN) { s = 0; ph ^= 1; }
-                }
             }
         }
     }
