@@ -74,6 +74,8 @@ def lib():
     L.bertx_selftest_gemm.argtypes = [c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, pf, pf]
     L.bertx_bench_gemm.restype = c_i32
     L.bertx_bench_gemm.argtypes = [c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, pf]
+    L.bertx_bench_attention.restype = c_i32
+    L.bertx_bench_attention.argtypes = [c_i32, c_i32, c_i32, c_i32, c_i32, pf]
     L.bertx_selftest_attention.restype = c_i32
     L.bertx_selftest_attention.argtypes = [c_i32, c_i32, c_i32, c_i32, c_i32, pf, pf]
     _lib = L
@@ -206,6 +208,16 @@ def selftest_attention(n_sent, max_len, n_head, d_head, seed=0):
     err, ref = ctypes.c_float(0), ctypes.c_float(0)
     rc = lib().bertx_selftest_attention(n_sent, max_len, n_head, d_head, seed, ctypes.byref(err), ctypes.byref(ref))
     return rc, err.value, ref.value
+
+
+def bench_attention(n_sent, length, n_head, d_head, reps=10):
+    """(ms per launch, TFLOP/s) of the attention kernel on n_sent sentences of `length` tokens."""
+    ms = ctypes.c_float(0)
+    rc = lib().bertx_bench_attention(n_sent, length, n_head, d_head, reps, ctypes.byref(ms))
+    if rc != 0:
+        raise RuntimeError(f"bertx_bench_attention failed ({rc})")
+    per = ms.value / reps
+    return per, 4.0 * n_sent * length * length * n_head * d_head / (per * 1e-3) / 1e12
 
 
 def bench_gemm(M, N, K, wtype, epilogue, reps=20):

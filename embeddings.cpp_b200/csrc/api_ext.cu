@@ -280,4 +280,47 @@ int32_t bertx_selftest_attention(int32_t n_sent, int32_t max_len, int32_t n_head
     return compare_h(o1.as<__half>(), o2.as<__half>(), T * H, max_abs_err, max_ref) ? 0 : -8;
 }
 
+int32_t bertx_bench_attention(int32_t n_sent, int32_t len, int32_t n_head, int32_t d_head, int32_t reps, float * ms_total) {
+    if (n_sent <= 0 || len <= 0 || reps <= 0 || (d_head != 32 && d_head != 64)) return -1;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { fprintf(stderr, "bertx_bench_attention: no CUDA device\n"); return -2; }
+    cudaDeviceProp prop; cudaGetDeviceProperties(&prop, 0);
+    const int H = n_head * d_head;
+    const size_t T = (size_t) n_sent * len;
+    std::vector<int32_t> cu(n_sent + 1);
+    for (int i = 0; i <= n_sent; ++i) cu[i] = i * len;
+    // 1 MiB of random fp16 tiled over the buffer is enough for timing
+    std::mt19937 rng(7);
+    std::normal_distribution<float> nd(0.f, 1.f);
+    std::vector<uint16_t> chunk(1 << 19);
+    for (auto & v : chunk) v = f2h_bits(nd(rng));
+    DevBuf qkv, dcu, o1;
+    const size_t nbytes = T * 3 * H * 2;
+    if (!qkv.alloc(nbytes) || !dcu.alloc(cu.size() * 4) || !o1.alloc(T * H * 2)) return -3;
+    for (size_t off = 0; off < nbytes; off += chunk.size() * 2) {
+        const size_t n = std::min(chunk.size() * 2, nbytes - off);
+        cudaMemcpy((char *) qkv.p + off, chunk.data(), n, cudaMemcpyHostToDevice);
+    }
+    cudaMemcpy(dcu.p, cu.data(), cu.size() * 4, cudaMemcpyHostToDevice);
+    CUtensorMap tq, tkv;
+    if (d_head == 64 && !make_attention_tmaps(&tq, &tkv, qkv.as<__half>(), T, H)) return -4;
+    auto launch = [&]() {
+        return d_head == 64
+            ? launch_attention_tc(&tq, &tkv, dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, prop.multiProcessorCount, 0)
+            : launch_attention(qkv.as<__half>(), dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, 0);
+    };
+    if (!cuda_ok(launch(), "bench attention launch") || !cuda_ok(cudaDeviceSynchronize(), "bench attention")) return -6;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    cudaEventRecord(e0, 0);
+    for (int i = 0; i < reps; ++i) launch();
+    cudaEventRecord(e1, 0);
+    const bool ok = cuda_ok(cudaDeviceSynchronize(), "bench attention");
+    float ms = 0.f;
+    if (ok) cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    *ms_total = ms;
+    return ok ? 0 : -6;
+}
+
 }  // extern "C"

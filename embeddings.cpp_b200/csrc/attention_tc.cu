@@ -44,10 +44,11 @@ struct AttnTcParams {
     float scale_log2;
 };
 
-struct Item { int t0, len, q0, head; bool valid; };
+struct Item { int t0, len, q0, head; __device__ __forceinline__ bool valid() const { return q0 < len; } };
 
-__device__ __forceinline__ Item decode_item(const AttnTcParams & p, int item) {
+__device__ __forceinline__ Item decode_item(const AttnTcParams & p, int item, int total) {
     Item it;
+    if (item >= total) { it.t0 = it.len = it.q0 = it.head = 0; return it; }
     const int qt = item % p.max_qt;
     const int hs = item / p.max_qt;
     it.head = hs % p.n_head;
@@ -55,9 +56,27 @@ __device__ __forceinline__ Item decode_item(const AttnTcParams & p, int item) {
     it.t0 = __ldg(p.cu + sent);
     it.len = __ldg(p.cu + sent + 1) - it.t0;
     it.q0 = qt * AQ;
-    it.valid = it.q0 < it.len;
     return it;
 }
+
+// Round-robin item walk with the NEXT item's sentence bounds (two dependent-free global loads)
+// fetched while the current item is processed, so their latency is off the critical path.
+struct ItemWalk {
+    int next_item, total, stride;
+    Item cur, nxt;
+    __device__ __forceinline__ ItemWalk(const AttnTcParams & p, int first, int stride_, int total_)
+        : next_item(first), total(total_), stride(stride_) {
+        nxt = decode_item(p, next_item, total);
+    }
+    // moves to the next item of this CTA; false when the walk is over
+    __device__ __forceinline__ bool advance(const AttnTcParams & p) {
+        if (next_item >= total) return false;
+        cur = nxt;
+        next_item += stride;
+        nxt = decode_item(p, next_item, total);
+        return true;
+    }
+};
 
 __device__ __forceinline__ float ex2f(float x) {
     float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y;
@@ -109,9 +128,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         // ------------------------------------------------------------ TMA producer
         if (lane == 0) {
             uint32_t kv_it = 0, item_n = 0;
-            for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
-                const Item it = decode_item(p, item);
-                if (!it.valid) continue;
+            ItemWalk walk(p, blockIdx.x, gridDim.x, total_items);
+            while (walk.advance(p)) {
+                const Item it = walk.cur;
+                if (!it.valid()) continue;
                 const int nb = (it.len + AK - 1) / AK;
                 mbar_wait(q_empty, (item_n & 1) ^ 1);
                 mbar_expect_tx(q_full, kQBytes);
@@ -131,9 +151,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         constexpr uint32_t idesc_s = umma_idesc_f16(AQ, AK);            // Q (K-major) x K (K-major)
         constexpr uint32_t idesc_o = umma_idesc_f16(AQ, AD, 1);         // P (TMEM) x V (MN-major)
         uint32_t g = 0, item_n = 0;                                     // g: running key-block counter
-        for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
-            const Item it = decode_item(p, item);
-            if (!it.valid) continue;
+        ItemWalk walk(p, blockIdx.x, gridDim.x, total_items);
+        while (walk.advance(p)) {
+            const Item it = walk.cur;
+            if (!it.valid()) continue;
             const int nb = (it.len + AK - 1) / AK;
             mbar_wait(q_full, item_n & 1);
             tc_fence_after_sync();
@@ -182,9 +203,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         const int row = q * 32 + lane;                        // query row inside the tile
         const uint32_t lane_base = tmem_base + ((uint32_t) (q * 32) << 16);
         uint32_t g = 0;
-        for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
-            const Item it = decode_item(p, item);
-            if (!it.valid) continue;
+        ItemWalk walk(p, blockIdx.x, gridDim.x, total_items);
+        while (walk.advance(p)) {
+            const Item it = walk.cur;
+            if (!it.valid()) continue;
             const int nb = (it.len + AK - 1) / AK;
             float m_ref = -INFINITY, l = 0.f;
             for (int b = 0; b < nb; ++b) {
@@ -217,30 +239,28 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                     mbar_wait(pv_done, (gb - 1) & 1);
                     if (__any_sync(0xffffffffu, need)) {
                         tc_fence_after_sync();
-                        uint32_t o0[32], o1[32];
-                        tmem_ld_32x32b_x32(lane_base + TM_O, o0);
-                        tmem_ld_32x32b_x32(lane_base + TM_O + 32, o1);
-                        tmem_ld_wait();
+#pragma unroll 1
+                        for (int hh = 0; hh < 2; ++hh) {          // 32 columns at a time: this path is rare, keep it lean in registers
+                            uint32_t o[32];
+                            tmem_ld_32x32b_x32(lane_base + TM_O + hh * 32, o);
+                            tmem_ld_wait();
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            o0[j] = __float_as_uint(__uint_as_float(o0[j]) * factor);
-                            o1[j] = __float_as_uint(__uint_as_float(o1[j]) * factor);
+                            for (int j = 0; j < 32; ++j) o[j] = __float_as_uint(__uint_as_float(o[j]) * factor);
+                            tmem_st_32x32b_x32(lane_base + TM_O + hh * 32, o);
                         }
-                        tmem_st_32x32b_x32(lane_base + TM_O, o0);
-                        tmem_st_32x32b_x32(lane_base + TM_O + 32, o1);
                     }
                 }
-                const float nm = -m_ref;
-                float sum = 0.f;
+                const float2 nm2 = make_float2(-m_ref, -m_ref), sc2 = make_float2(p.scale_log2, p.scale_log2);
+                float2 sum[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
                 uint32_t pk[32];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
-                    const float p0 = ex2f(fmaf(s[2 * j], p.scale_log2, nm));
-                    const float p1 = ex2f(fmaf(s[2 * j + 1], p.scale_log2, nm));
-                    sum += p0 + p1;
-                    pk[j] = pack_h2(p0, p1);
+                    const float2 x = __ffma2_rn(make_float2(s[2 * j], s[2 * j + 1]), sc2, nm2);
+                    const float2 e = make_float2(ex2f(x.x), ex2f(x.y));
+                    sum[j & 1] = __fadd2_rn(sum[j & 1], e);
+                    pk[j] = pack_h2(e.x, e.y);
                 }
-                l += sum;
+                l += (sum[0].x + sum[0].y) + (sum[1].x + sum[1].y);
                 tmem_st_32x32b_x32(s_addr, pk);               // P over the first half of this S buffer
                 tmem_st_wait();
                 tc_fence_before_sync();

@@ -67,6 +67,11 @@ BERT_API int32_t bertx_bench_gemm(int32_t M, int32_t N, int32_t K, int32_t wtype
 BERT_API int32_t bertx_selftest_attention(int32_t n_sent, int32_t max_len, int32_t n_head, int32_t d_head,
                                           int32_t seed, float * max_abs_err, float * max_ref);
 
+/* Time `reps` back-to-back launches of the production attention kernel over n_sent sentences of
+ * exactly len tokens (random q/k/v, CUDA events). */
+BERT_API int32_t bertx_bench_attention(int32_t n_sent, int32_t len, int32_t n_head, int32_t d_head, int32_t reps,
+                                       float * ms_total);
+
 #ifdef __cplusplus
 }
 #endif
