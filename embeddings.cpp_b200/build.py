@@ -18,6 +18,8 @@ LIB = os.path.join(HERE, "lib")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
          "-Xcompiler", "-fPIC,-fvisibility=hidden,-pthread", "-I", os.path.join(HERE, "..", "include")]
+if os.environ.get("BERT_DEBUG_WAIT"):
+    FLAGS.append("-DBERT_DEBUG_WAIT")
 SOURCES = ["gemm_tc.cu", "attention.cu", "attention_tc.cu", "rowwise.cu", "upload.cu", "engine_load.cu", "engine_run.cu",
            "api.cu", "api_ext.cu", "tokenizer.cpp", "model_file.cpp"]
 

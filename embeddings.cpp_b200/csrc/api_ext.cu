@@ -204,6 +204,19 @@ static int32_t gemm_test_impl(int32_t M, int32_t N, int32_t K, int32_t wtype, in
     if (!make_tmap_f16_2d(&tmo, o1.p, M, N, 32)) return -4;        // exactly M rows: the store must clip the tail tile
     const int fq = wtype == W_Q4_1 ? W_Q4_1 : W_Q4_0;
     GemmArgs g1{&tma, &tmo, &tmr, a.as<__half>(), &w, res.as<__half>(), o1.as<__half>(), M, epilogue, fq};
+    DevBuf o1q, lng, lnb;
+    CUtensorMap tmo2;
+    if (epilogue & EPI_LN) {
+        std::vector<float> hg(N), hb(N);
+        for (auto & v : hg) v = 1.0f + 0.2f * nd(rng);
+        for (auto & v : hb) v = 0.3f * nd(rng);
+        if (!o1q.alloc((size_t) M * N * 2) || !lng.alloc((size_t) N * 4) || !lnb.alloc((size_t) N * 4)) return -3;
+        cudaMemcpy(lng.p, hg.data(), (size_t) N * 4, cudaMemcpyHostToDevice);
+        cudaMemcpy(lnb.p, hb.data(), (size_t) N * 4, cudaMemcpyHostToDevice);
+        cudaMemset(o1q.p, 0xFF, (size_t) M * N * 2);
+        if (!make_tmap_f16_2d(&tmo2, o1q.p, M, N, 32)) return -4;
+        g1.tmap_out2 = &tmo2; g1.ln_gamma = lng.as<float>(); g1.ln_beta = lnb.as<float>();
+    }
     GemmArgs g2 = g1; g2.out = o2.as<__half>();
     if (!cuda_ok(launch_gemm_tc(g1, prop.multiProcessorCount, 0), "selftest gemm_tc launch")) return -6;
     if (!cuda_ok(cudaDeviceSynchronize(), "selftest gemm_tc")) return -6;
@@ -219,6 +232,21 @@ static int32_t gemm_test_impl(int32_t M, int32_t N, int32_t K, int32_t wtype, in
         cudaEventDestroy(e0); cudaEventDestroy(e1);
         *ms_out = ms;
         return ok ? 0 : -6;
+    }
+    if (epilogue & EPI_LN) {
+        // reference for the fused LayerNorm epilogue: SIMT GEMM (+bias +residual) -> y, then the row kernel
+        DevBuf y2, o2q;
+        if (!y2.alloc((size_t) M * N * 2) || !o2q.alloc((size_t) M * N * 2)) return -3;
+        g2.out = y2.as<__half>(); g2.epilogue = EPI_BIAS | EPI_RESIDUAL;
+        if (!cuda_ok(launch_gemm_simt(g2, 0), "selftest gemm_simt launch")) return -7;
+        if (!cuda_ok(launch_ln(y2.as<__half>(), lng.as<float>(), lnb.as<float>(), M, N, o2.as<__half>(),
+                               (epilogue & EPI_FAKEQUANT) ? o2q.as<__half>() : nullptr, fq, 0), "selftest ln launch")) return -7;
+        if (!cuda_ok(cudaDeviceSynchronize(), "selftest gemm_simt + ln")) return -7;
+        float e1 = 0.f, r1 = 0.f, e2 = 0.f, r2 = 0.f;
+        if (!compare_h(o1.as<__half>(), o2.as<__half>(), (size_t) M * N, &e1, &r1)) return -8;
+        if ((epilogue & EPI_FAKEQUANT) && !compare_h(o1q.as<__half>(), o2q.as<__half>(), (size_t) M * N, &e2, &r2)) return -8;
+        *max_abs_err = e1 > e2 ? e1 : e2; *max_ref = r1 > r2 ? r1 : r2;
+        return 0;
     }
     if (!cuda_ok(launch_gemm_simt(g2, 0), "selftest gemm_simt launch")) return -7;
     if (!cuda_ok(cudaDeviceSynchronize(), "selftest gemm_simt")) return -7;

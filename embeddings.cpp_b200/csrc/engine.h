@@ -48,6 +48,7 @@ struct Replica {
     CUtensorMap tm_xin, tm_ctx, tm_x1in, tm_mid;     // A-operand maps (box 64 x 128)
     CUtensorMap to_qkv, to_y, to_mid;                // output maps (box 64 x 32, epilogue TMA stores)
     CUtensorMap ta_q, ta_kv;                         // attention maps over qkv (box 64 x 128 / 64 x 64)
+    CUtensorMap to_x, to_xq, to_x1, to_x1q;          // outputs of the GEMMs with fused LayerNorm (box 64 x 32)
     CUtensorMap tr_x, tr_x1;                         // residual maps (box 64 x 32, epilogue TMA loads)
     static const int kSlots = 2;
     int32_t * d_ids[kSlots] = {nullptr, nullptr};    // [t_cap]
@@ -80,7 +81,9 @@ struct Engine {
     std::mutex mu;                             // a context is not re-entrant (bert.h note)
     std::atomic<int64_t> launches{0};
     int fq_type = -1;                          // W_Q4_0 / W_Q4_1 when activation fake-quant is on
-    bool gemm_simt = false, attn_ref = false, attn_mma = false;  // validation kernels forced by env (debug only)
+    bool gemm_simt = false, attn_ref = false, attn_mma = false;
+    bool fuse_ln_att = true;                   // also fuse the LayerNorm after the attention-output GEMM (BERT_FUSE_LN=1: ffn-out only)
+    bool fuse_ln = true;                       // LayerNorm in the epilogue of the o / ffn-out GEMMs (BERT_FUSE_LN=0 disables)  // validation kernels forced by env (debug only)
     int t_cap = 0, b_cap = 0;
 
     ~Engine();

@@ -182,6 +182,7 @@ bool Engine::init_devices(const ModelFile & mf) {
     if (devs.empty()) for (int i = 0; i < n_dev; ++i) devs.push_back(i);
 
     if (const char * e = getenv("BERT_GEMM_IMPL")) gemm_simt = strcmp(e, "simt") == 0;
+    if (const char * e = getenv("BERT_FUSE_LN")) { fuse_ln = atoi(e) != 0; fuse_ln_att = atoi(e) >= 2; }
     if (const char * e = getenv("BERT_ATTN_IMPL")) { attn_ref = strcmp(e, "ref") == 0; attn_mma = strcmp(e, "mma") == 0; }
     fq_type = (hp.ftype == W_Q4_0 || hp.ftype == W_Q4_1) ? hp.ftype : -1;
     if (const char * e = getenv("BERT_ACT_QUANT")) { if (atoi(e) == 0) fq_type = -1; }
@@ -335,6 +336,8 @@ bool Engine::alloc_workspace(Replica & r) {
         !make_tmap_f16_2d(&r.to_qkv, r.qkv, rows, 3 * H, 32) || !make_tmap_f16_2d(&r.to_y, r.y, rows, H, 32) ||
         !make_tmap_f16_2d(&r.to_mid, r.mid, rows, I, 32) ||
         !make_attention_tmaps(&r.ta_q, &r.ta_kv, r.qkv, rows, H) ||
+        !make_tmap_f16_2d(&r.to_x, r.x, rows, H, 32) || !make_tmap_f16_2d(&r.to_xq, r.xq, rows, H, 32) ||
+        !make_tmap_f16_2d(&r.to_x1, r.x1, rows, H, 32) || !make_tmap_f16_2d(&r.to_x1q, r.x1q, rows, H, 32) ||
         !make_tmap_f16_2d(&r.tr_x, r.x, rows, H, 32) || !make_tmap_f16_2d(&r.tr_x1, r.x1, rows, H, 32)) {
         fprintf(stderr, "bert_load_from_file: cuTensorMapEncodeTiled failed for an activation map\n");
         return false;

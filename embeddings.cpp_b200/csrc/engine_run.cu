@@ -52,6 +52,16 @@ bool Engine::forward(Replica & r, const int32_t * d_ids, const int32_t * d_cu, i
         end();
     };
 
+    // o / ffn-out GEMM with the LayerNorm that follows it fused into the epilogue (no y round trip)
+    auto gemm_ln = [&](const CUtensorMap * tm, const __half * a, const DevWeight & w, const __half * res,
+                       const CUtensorMap * tmr, const float * g_, const float * b_, __half * out,
+                       const CUtensorMap * tmo, const CUtensorMap * tmo2) {
+        GemmArgs g{tm, tmo, tmr, a, &w, res, out, T, EPI_BIAS | EPI_RESIDUAL | EPI_LN | (fq ? EPI_FAKEQUANT : 0), fq_type};
+        g.tmap_out2 = fq ? tmo2 : nullptr; g.ln_gamma = g_; g.ln_beta = b_;
+        begin(KK_GEMM);
+        L(KK_GEMM, launch_gemm_tc(g, r.num_sms, st), "gemm+ln");
+        end();
+    };
     begin(KK_EMBED);
     L(KK_EMBED, launch_embed_ln(r.word, r.postype, r.ln_e_g, r.ln_e_b, d_ids, d_cu, n_sent, T, H,
                                 r.x, fq ? r.xq : nullptr, fq_type, st), "embed_ln");
@@ -69,15 +79,24 @@ bool Engine::forward(Replica & r, const int32_t * d_ids, const int32_t * d_cu, i
             L(KK_ATTN, ae, "attention");
         }
         end();
-        gemm(&r.tm_ctx, &r.to_y, r.ctx, ly.o, r.x, &r.tr_x, r.y, EPI_BIAS | EPI_RESIDUAL);
-        begin(KK_LN);
-        L(KK_LN, launch_ln(r.y, ly.ln_att_g, ly.ln_att_b, T, H, r.x1, fq ? r.x1q : nullptr, fq_type, st), "ln_att");
-        end();
+        const bool fuse = fuse_ln && !gemm_simt && gemm_ln_fusable(ly.o) && gemm_ln_fusable(ly.ffo);
+        if (fuse && fuse_ln_att) {
+            gemm_ln(&r.tm_ctx, r.ctx, ly.o, r.x, &r.tr_x, ly.ln_att_g, ly.ln_att_b, r.x1, &r.to_x1, &r.to_x1q);
+        } else {
+            gemm(&r.tm_ctx, &r.to_y, r.ctx, ly.o, r.x, &r.tr_x, r.y, EPI_BIAS | EPI_RESIDUAL);
+            begin(KK_LN);
+            L(KK_LN, launch_ln(r.y, ly.ln_att_g, ly.ln_att_b, T, H, r.x1, fq ? r.x1q : nullptr, fq_type, st), "ln_att");
+            end();
+        }
         gemm(&r.tm_x1in, &r.to_mid, r.x1q, ly.ffi, nullptr, nullptr, r.mid, EPI_BIAS | EPI_GELU | (fq ? EPI_FAKEQUANT : 0));
-        gemm(&r.tm_mid, &r.to_y, r.mid, ly.ffo, r.x1, &r.tr_x1, r.y, EPI_BIAS | EPI_RESIDUAL);
-        begin(KK_LN);
-        L(KK_LN, launch_ln(r.y, ly.ln_out_g, ly.ln_out_b, T, H, r.x, fq ? r.xq : nullptr, fq_type, st), "ln_out");
-        end();
+        if (fuse) {
+            gemm_ln(&r.tm_mid, r.mid, ly.ffo, r.x1, &r.tr_x1, ly.ln_out_g, ly.ln_out_b, r.x, &r.to_x, &r.to_xq);
+        } else {
+            gemm(&r.tm_mid, &r.to_y, r.mid, ly.ffo, r.x1, &r.tr_x1, r.y, EPI_BIAS | EPI_RESIDUAL);
+            begin(KK_LN);
+            L(KK_LN, launch_ln(r.y, ly.ln_out_g, ly.ln_out_b, T, H, r.x, fq ? r.xq : nullptr, fq_type, st), "ln_out");
+            end();
+        }
     }
     begin(KK_POOL);
     L(KK_POOL, launch_pool_norm(r.x, d_cu, n_sent, H, d_out, st), "pool_norm");

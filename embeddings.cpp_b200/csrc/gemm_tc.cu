@@ -23,7 +23,7 @@ constexpr int BK = 64;
 constexpr int UMMA_K = 16;
 constexpr int kSmemLimit = 232448;                   // 227 KB opt-in limit per CTA
 
-template <int BN, int WT> struct GemmCfg {
+template <int BN, int WT, bool LN> struct GemmCfg {
     static constexpr bool kQ4      = WT != W_F16;
     static constexpr int kBHalf    = BN / 2;                 // B rows this CTA supplies
     static constexpr int kABytes   = BM * BK * 2;
@@ -35,23 +35,31 @@ template <int BN, int WT> struct GemmCfg {
     static constexpr int kAccStride = BN <= 64 ? 64 : (BN <= 128 ? 128 : 256);
     static constexpr int kOutBytes = 8 * 4096;          // 8 epilogue warps x [32 rows][128 B] staging for TMA stores
     static constexpr int kResBytes = 8 * 4096;          // same geometry, residual boxes prefetched by TMA
-    static constexpr int kBiasBytes = 8 * 256;          // per warp: the 64 bias values of its current box
+    static constexpr int kBiasBytes = LN ? 0 : 8 * 256; // per warp: the 64 bias values of its current box
+    // fused LayerNorm: per-row partial statistics of up to 3 pairs x 2 warps, double-buffered, plus the
+    // CTA's 256-column slices of bias / gamma / beta
+    static constexpr int kLnMaxPairs = 3;
+    static constexpr int kLnStatBytes = LN ? 2 * kLnMaxPairs * 2 * BM * 8 : 0;
+    static constexpr int kLnParamBytes = LN ? 3 * BN * 4 : 0;
     static constexpr int kBarBytes = 512;
-    static constexpr int kFixed = kOutBytes + kResBytes + kBiasBytes + 1024 /*align slack*/ + kBarBytes;
+    static constexpr int kFixed = kOutBytes + kResBytes + kBiasBytes + kLnStatBytes + kLnParamBytes + 1024 /*align slack*/ + kBarBytes;
     // fp16 weights: A and B travel together through one ring.  q4 weights: A needs TMA-latency depth,
     // the dequantised B only a short ring (it is produced from smem), the 4-bit ring hides L2 latency.
     static constexpr int kFitF16   = (kSmemLimit - kFixed) / (kABytes + kBBytes);
-    static constexpr int kSA       = kQ4 ? 5 : (kFitF16 > 6 ? 6 : kFitF16);
+    static constexpr int kSA       = kQ4 ? (LN ? 4 : 5) : (kFitF16 > 6 ? 6 : kFitF16);
     static constexpr int kSB       = kQ4 ? 3 : kSA;
+    // (the 4-bit ring depth stays a multiple of the number of dequant groups, so a slot is always
+    // refilled for the same group that drained it)
     static constexpr int kSN       = kQ4 ? 6 : 0;
     static constexpr int kSmemBytes = kSA * kABytes + kSB * kBBytes + kSN * kNibSlot + kFixed;
     static_assert(kSmemBytes <= kSmemLimit, "shared memory budget");
-    static_assert(2 * kSA + 2 * kSB + 2 * kSN + 12 <= (kBarBytes - 8) / 8, "barrier region");
+    static_assert(2 * kSA + 2 * kSB + 2 * kSN + 13 <= (kBarBytes - 8) / 8, "barrier region");
 };
 
 struct GemmParams {
     const uint4 * qnib; const __half * qd; const __half * qm;
     const float * bias; __half * out;
+    const float * ln_gamma; const float * ln_beta;       // fused LayerNorm (EPI_LN)
     int M, N, K, epilogue, fq_type;
 };
 
@@ -65,17 +73,19 @@ __device__ __forceinline__ float rcp_approx(float x) {
 __device__ __forceinline__ float2 round_h2(float2 v) {
     return __half22float2(__floats2half2_rn(v.x, v.y));
 }
-// Reference GELU numerics: y = f16(gelu_f32(f16(x))) through a 64K-entry table
-// (ggml.c:3561-3580, 4332).  tanh-GELU rewritten as f / (1 + exp(-2u)), u = sqrt(2/pi) f (1 + 0.044715 f^2),
-// with ex2.approx / rcp.approx (2 MUFU per element) and packed f32x2 arithmetic.
+// Reference GELU numerics: y = f16(gelu_f32(f16(x))) through a 64K-entry table (ggml.c:3561-3580, 4332),
+// gelu(x) = 0.5 x (1 + tanh(sqrt(2/pi) x (1 + 0.044715 x^2))).  One MUFU.TANH per element (abs. error
+// ~2^-11, below the table's own f16 output rounding for |x| < 8) and packed f32x2 arithmetic.
+__device__ __forceinline__ float tanh_approx(float x) {
+    float y; asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x)); return y;
+}
 __device__ __forceinline__ float2 gelu2_ref_numerics(float2 v) {
-    const float c1 = -2.0f * 1.4426950408889634f * 0.79788456080286535588f;
-    const float c2 = c1 * 0.044715f;
+    const float k1 = 0.79788456080286535588f, k2 = 0.79788456080286535588f * 0.044715f;
     const float2 f = round_h2(v);
-    const float2 p = __ffma2_rn(__fmul2_rn(f, f), make_float2(c2, c2), make_float2(c1, c1));
-    const float2 z = __fmul2_rn(f, p);
-    const float2 d = __fadd2_rn(make_float2(ex2_approx(z.x), ex2_approx(z.y)), make_float2(1.f, 1.f));
-    return round_h2(__fmul2_rn(f, make_float2(rcp_approx(d.x), rcp_approx(d.y))));
+    const float2 u = __fmul2_rn(f, __ffma2_rn(__fmul2_rn(f, f), make_float2(k2, k2), make_float2(k1, k1)));
+    const float2 t = make_float2(tanh_approx(u.x), tanh_approx(u.y));
+    const float2 h = __fmul2_rn(f, make_float2(0.5f, 0.5f));
+    return round_h2(__ffma2_rn(h, t, h));
 }
 // q8 fake-quant of 32 consecutive values (16 float2) held by one thread; rint via the
 // 1.5*2^23 magic constant (round-half-even, |x| <= 127 here) to stay on the FMA pipe
@@ -125,13 +135,21 @@ __device__ __forceinline__ uint32_t dq_pair(uint32_t w, int i, __half2 d2, __hal
     return *reinterpret_cast<uint32_t *>(&h);
 }
 
-// Tile walk shared by all roles: cluster `cid` of `ncl` takes tiles cid, cid + ncl, ...;
-// tile -> (m block of 256 rows, n block of BN columns), n fastest so that concurrently
-// running clusters share A rows through L2.
+// Tile walk shared by all roles.  Plain GEMM: cluster (= CTA pair) `cid` of `ncl` takes tiles cid,
+// cid + ncl, ...; tile -> (m block of 256 rows, n block of BN columns), n fastest so that concurrently
+// running pairs share A rows through L2.  Fused LayerNorm: a cluster holds N/BN pairs and takes whole
+// 256-row stripes cid, cid + ncl, ...; pair `pair` of the cluster always computes n block `pair`.
 struct TileWalk {
-    int num_n, num_tiles, cid, ncl;
-    __device__ __forceinline__ int my_tiles() const { return cid < num_tiles ? (num_tiles - cid + ncl - 1) / ncl : 0; }
-    __device__ __forceinline__ int tile(int i) const { return cid + i * ncl; }
+    int num_n, num_m, cid, ncl, pair;
+    bool stripes;
+    __device__ __forceinline__ int my_tiles() const {
+        const int total = stripes ? num_m : num_m * num_n;
+        return cid < total ? (total - cid + ncl - 1) / ncl : 0;
+    }
+    __device__ __forceinline__ void get(int i, int & m_blk, int & n_blk) const {
+        const int t = cid + i * ncl;
+        if (stripes) { m_blk = t; n_blk = pair; } else { m_blk = t / num_n; n_blk = t % num_n; }
+    }
 };
 
 constexpr int DQ_GROUPS = 2;                       // dequant warp groups; group g takes k-stages g, g + 2, ...
@@ -142,14 +160,16 @@ constexpr int DQ_GROUP_WARPS = DQ_WARPS / DQ_GROUPS;
 //   warps 12-19 q4 dequant (two warpgroups; absent for fp16 weights)
 constexpr int CTRL_WARPS = 4;
 template <int WT> constexpr int gemm_threads() { return 32 * (CTRL_WARPS + EPI_WARPS + (WT == W_F16 ? 0 : DQ_WARPS)); }
-constexpr int kRegsCtrl = 40, kRegsDequant = 56, kRegsEpilogue = 160;     // q4: 640 threads launch with 96
+constexpr int kRegsCtrl = 40;                                            // q4: 640 threads launch with 96
+template <bool LN> struct RegBudget { static constexpr int kDequant = 56, kEpilogue = 160; };
 
-template <int BN, int WT>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(gemm_threads<WT>(), 1)
+// Launched with a runtime cluster dimension: 2 (one CTA pair) or, with fused LayerNorm, 2 * N / BN.
+template <int BN, int WT, bool LN>
+__global__ void __launch_bounds__(gemm_threads<WT>(), 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
-               const GemmParams p) {
-    using Cfg = GemmCfg<BN, WT>;
+               const __grid_constant__ CUtensorMap tmap_out2, const GemmParams p) {
+    using Cfg = GemmCfg<BN, WT, LN>;
     constexpr bool Q4 = Cfg::kQ4;
     constexpr int SA = Cfg::kSA, SB = Cfg::kSB, SN = Cfg::kSN;
     constexpr int NB = BN / 64;                               // 64-column output boxes per tile
@@ -161,7 +181,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     uint8_t * smem_res = smem_out + Cfg::kOutBytes;           // 8 warps x 4 KB residual boxes
     uint8_t * smem_bias = smem_res + Cfg::kResBytes;          // 8 warps x 64 floats
     uint8_t * smem_nib = smem_bias + Cfg::kBiasBytes;         // SN x 4-bit weight stages (q4 only)
-    uint64_t * bars = (uint64_t *) (smem_nib + SN * Cfg::kNibSlot);
+    uint8_t * smem_lnstat = smem_nib + SN * Cfg::kNibSlot;    // LN: [2][pairs<=3][2][128] x (mean, M2)
+    uint8_t * smem_lnpar = smem_lnstat + Cfg::kLnStatBytes;   // LN: bias | gamma | beta of this CTA's BN columns
+    uint64_t * bars = (uint64_t *) (smem_lnpar + Cfg::kLnParamBytes);
     uint64_t * a_full = bars;                   // [SA]  leader's copy is live (A of both CTAs; + B for fp16 weights)
     uint64_t * a_empty = a_full + SA;           // [SA]  per CTA, multicast commit
     uint64_t * b_full = a_empty + SA;           // [SB]  q4: leader's copy, dequant warps of both CTAs arrive
@@ -171,15 +193,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     uint64_t * tfull = n_empty + SN;            // [2]   per CTA, multicast commit
     uint64_t * tempty = tfull + 2;              // [2]   leader's copy is live: 16 epilogue warps arrive
     uint64_t * rfull = tempty + 2;              // [8] residual box, per epilogue warp
-    uint32_t * tmem_slot = (uint32_t *) (rfull + 8);
+    uint64_t * ln_bar = rfull + 8;              // [1] LN: partial statistics of all pairs have landed
+    uint32_t * tmem_slot = (uint32_t *) (ln_bar + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t rank = cluster_ctarank();                  // 0 = leader (issues the MMAs)
+    const uint32_t crank = cluster_ctarank();                 // rank in the cluster
+    const uint32_t rank = crank & 1;                          // rank in the CTA pair, 0 = leader (issues the MMAs)
+    const uint32_t leader = crank & ~1u;                      // cluster rank of this pair's leader
+    const uint16_t pair_mask = (uint16_t) (3u << leader);
     TileWalk tw;
     tw.num_n = p.N / BN;
-    tw.num_tiles = ((p.M + 2 * BM - 1) / (2 * BM)) * tw.num_n;
+    tw.num_m = (p.M + 2 * BM - 1) / (2 * BM);
     tw.cid = (int) cluster_id_x();
     tw.ncl = (int) cluster_nctaid_x();
+    tw.pair = (int) (crank >> 1);
+    tw.stripes = LN;
     const int my_tiles = tw.my_tiles();
     const int num_k = p.K / BK;
 
@@ -195,6 +223,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         }
         for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 2 * EPI_WARPS); }
         for (int i = 0; i < 8; ++i) mbar_init(&rfull[i], 1);
+        if (LN) mbar_init(ln_bar, (uint32_t) tw.num_n * EPI_WARPS * 32);
         fence_mbar_init();
     }
     if (warp == 1) { tmem_alloc_pair(tmem_slot, Cfg::kTmemCols); tmem_relinquish_pair(); }
@@ -209,12 +238,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       if (warp == 0) {
         // ------------------------------------------------------------ TMA producer (both CTAs)
         if (lane == 0) {
-            const uint32_t full_leader = mapa_u32(smem_u32(&a_full[0]), 0);
+            const uint32_t full_leader = mapa_u32(smem_u32(&a_full[0]), leader);
             int s = 0; uint32_t ph = 0;
             for (int i = 0; i < my_tiles; ++i) {
-                const int tile = tw.tile(i);
-                const int m0 = (tile / tw.num_n) * (2 * BM) + (int) rank * BM;
-                const int nb0 = (tile % tw.num_n) * BN + (int) rank * Cfg::kBHalf;
+                int mb, nb; tw.get(i, mb, nb);
+                const int m0 = mb * (2 * BM) + (int) rank * BM;
+                const int nb0 = nb * BN + (int) rank * Cfg::kBHalf;
                 for (int kb = 0; kb < num_k; ++kb) {
                     mbar_wait(&a_empty[s], ph ^ 1);
                     if (rank == 0) mbar_expect_tx(&a_full[s], 2 * (Q4 ? Cfg::kABytes : Cfg::kABytes + Cfg::kBBytes));
@@ -247,9 +276,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             // +32 B per K=16 step inside the 128-B swizzle row (address field is >>4)
                             umma_f16_ss_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
                         }
-                        umma_commit_pair(&a_empty[sa]);                       // frees the stage in both CTAs
-                        if (Q4) umma_commit_pair(&b_empty[sb]);
-                        if (kb == num_k - 1) umma_commit_pair(&tfull[acc]);   // accumulators ready in both CTAs
+                        umma_commit_pair(&a_empty[sa], pair_mask);                       // frees the stage in both CTAs
+                        if (Q4) umma_commit_pair(&b_empty[sb], pair_mask);
+                        if (kb == num_k - 1) umma_commit_pair(&tfull[acc], pair_mask);   // accumulators ready in both CTAs
                     }
                     __syncwarp();
                     if (++sa == SA) { sa = 0; pha ^= 1; }
@@ -265,8 +294,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             int s = 0; uint32_t ph = 0;
             constexpr uint32_t kBytes = Cfg::kNibBytes + (WT == W_Q4_1 ? 2 : 1) * Cfg::kScaleBytes;
             for (int i = 0; i < my_tiles; ++i) {
-                const int tile = tw.tile(i);
-                const int nb0 = (tile % tw.num_n) * BN + (int) rank * Cfg::kBHalf;
+                int mb, nb; tw.get(i, mb, nb);
+                const int nb0 = nb * BN + (int) rank * Cfg::kBHalf;
                 for (int kb = 0; kb < num_k; ++kb) {
                     const size_t blk0 = ((size_t) kb * p.N + nb0) * 2;      // stage kb of rows nb0.. : [kb][n][2] blocks
                     uint8_t * slot = smem_nib + s * Cfg::kNibSlot;
@@ -281,7 +310,195 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         }
       }
     } else if (warp < CTRL_WARPS + EPI_WARPS) {
-      if constexpr (Q4) reg_alloc<kRegsEpilogue>();
+      if constexpr (Q4) reg_alloc<RegBudget<LN>::kEpilogue>();
+      if constexpr (LN) {
+        // ------------------------------------------------------------ epilogue with fused LayerNorm
+        // out = LN(acc + bias + residual) * gamma + beta, and its q8 fake-quantised twin (out2).
+        // The cluster's pairs hold the N/BN column blocks of one 256-row stripe.  Pass 1: each thread
+        // (one row, 64 * NBW columns) pulls its accumulators, adds bias + residual, rounds to fp16 (what
+        // the unfused path stores as y) and keeps the values in registers; the accumulator is released.
+        // The row's (mean, M2) partials go to every CTA holding the same rows through DSMEM; after the
+        // cluster-scope barrier they are merged (Chan) and pass 2 normalises out of registers.
+        static_assert(NB % 2 == 0, "fused LayerNorm needs an even number of boxes per tile");
+        constexpr int NBW = NB / 2;                // boxes per warp per tile
+        const int e = warp - CTRL_WARPS, q = warp & 3, half = e >> 2;
+        const int row = q * 32 + lane;             // row inside this CTA's 128
+        uint8_t * st = smem_out + e * 4096;
+        uint8_t * rs = smem_res + e * 4096;
+        uint64_t * rbar = rfull + e;
+        const float * s_bias = reinterpret_cast<const float *>(smem_lnpar);
+        const float * s_gamma = s_bias + BN;
+        const float * s_beta = s_gamma + BN;
+        const uint32_t tempty_leader = mapa_u32(smem_u32(&tempty[0]), leader);
+        const int npairs = tw.num_n;
+        const bool fq_on = (p.epilogue & EPI_FAKEQUANT) != 0;
+        // this CTA's column block is fixed (n block = pair): stage bias / gamma / beta once
+        {
+            const int t = threadIdx.x - 32 * CTRL_WARPS;                    // 0..255
+            float * par = reinterpret_cast<float *>(smem_lnpar);
+            for (int i = t; i < BN; i += 32 * EPI_WARPS) {
+                par[i] = __ldg(p.bias + tw.pair * BN + i);
+                par[BN + i] = __ldg(p.ln_gamma + tw.pair * BN + i);
+                par[2 * BN + i] = __ldg(p.ln_beta + tw.pair * BN + i);
+            }
+            asm volatile("bar.sync 1, %0;" :: "n"(32 * EPI_WARPS) : "memory");
+        }
+        auto res_load = [&](int it_) {
+            // first box of tile it_ -> residual buffer (lane 0 only)
+            int mb, nb; tw.get(it_, mb, nb);
+            mbar_expect_tx(rbar, 4096);
+            tma_load_2d(rs, &tmap_res, rbar, nb * BN + half * 64, mb * (2 * BM) + (int) rank * BM + q * 32);
+        };
+        if (my_tiles > 0 && lane == 0) res_load(0);
+        uint32_t rph = 0;                          // residual barrier phase
+        for (int it = 0; it < my_tiles; ++it) {
+            const int acc = it & 1;
+            const uint32_t acc_ph = (it >> 1) & 1;
+            int mb, nb; tw.get(it, mb, nb);
+            const int wrow0 = mb * (2 * BM) + (int) rank * BM + q * 32;
+            mbar_wait(&tfull[acc], acc_ph);
+            tc_fence_after_sync();
+            uint32_t hv[NBW][32];                  // pre-LN values as fp16 pairs
+#pragma unroll
+            for (int bi = 0; bi < NBW; ++bi) {
+                const int b = half + 2 * bi;
+                uint4 rr[8];
+                mbar_wait(rbar, rph); rph ^= 1;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) rr[c] = *reinterpret_cast<const uint4 *>(rs + lane * 128 + ((c ^ (lane & 7)) << 4));
+                uint32_t sink; asm volatile("mov.b32 %0, %1;" : "=r"(sink) : "r"(rr[7].w));
+                __syncwarp();
+                if (bi + 1 < NBW && lane == 0) {              // this tile's next box
+                    mbar_expect_tx(rbar, 4096);
+                    tma_load_2d(rs, &tmap_res, rbar, nb * BN + (b + 2) * 64, wrow0);
+                }
+#pragma unroll
+                for (int hh = 0; hh < 2; ++hh) {
+                    uint32_t r[32];
+                    tmem_ld_32x32b_x32(tmem_base + ((uint32_t) (q * 32) << 16) + acc * Cfg::kAccStride + b * 64 + hh * 32, r);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const float4 bb = *reinterpret_cast<const float4 *>(s_bias + b * 64 + hh * 32 + 4 * i);
+                        const __half2 * h = reinterpret_cast<const __half2 *>(&rr[hh * 4 + (i >> 1)]);
+                        const float2 r0 = __half22float2(h[(i & 1) * 2]), r1 = __half22float2(h[(i & 1) * 2 + 1]);
+                        float2 v0 = make_float2(__uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]));
+                        float2 v1 = make_float2(__uint_as_float(r[4 * i + 2]), __uint_as_float(r[4 * i + 3]));
+                        v0 = __fadd2_rn(__fadd2_rn(v0, make_float2(bb.x, bb.y)), r0);
+                        v1 = __fadd2_rn(__fadd2_rn(v1, make_float2(bb.z, bb.w)), r1);
+                        __half2 a0 = __floats2half2_rn(v0.x, v0.y), a1 = __floats2half2_rn(v1.x, v1.y);
+                        hv[bi][hh * 16 + 2 * i] = *reinterpret_cast<uint32_t *>(&a0);
+                        hv[bi][hh * 16 + 2 * i + 1] = *reinterpret_cast<uint32_t *>(&a1);
+                    }
+                }
+            }
+            // accumulator consumed: hand it back to the MMA issuer before the statistics exchange
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(tempty_leader + 8 * acc);
+            // ---- partial statistics over this thread's 64 * NBW values (two-pass, from the fp16 values)
+            float2 s2 = make_float2(0.f, 0.f);
+#pragma unroll
+            for (int bi = 0; bi < NBW; ++bi) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) s2 = __fadd2_rn(s2, __half22float2(*reinterpret_cast<const __half2 *>(&hv[bi][i])));
+            }
+            const float mean_p = (s2.x + s2.y) * (1.0f / (64 * NBW));
+            float2 m2 = make_float2(0.f, 0.f);
+            const float2 nmp = make_float2(-mean_p, -mean_p);
+#pragma unroll
+            for (int bi = 0; bi < NBW; ++bi) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const float2 dlt = __fadd2_rn(__half22float2(*reinterpret_cast<const __half2 *>(&hv[bi][i])), nmp);
+                    m2 = __ffma2_rn(dlt, dlt, m2);
+                }
+            }
+            const float M2_p = m2.x + m2.y;
+            // slot [parity][pair][half][row] in every CTA of the cluster with my pair rank
+            const int par = it & 1;
+            const uint32_t slot = smem_u32(smem_lnstat) + (uint32_t) ((((par * Cfg::kLnMaxPairs + tw.pair) * 2 + half) * BM + row) * 8);
+            const uint32_t lnb = smem_u32(ln_bar);
+            for (int pj = 0; pj < npairs; ++pj) {
+                const uint32_t dst = (uint32_t) (2 * pj) + rank;
+                st_cluster_f32x2(mapa_u32(slot, dst), mean_p, M2_p);
+                mbar_arrive_cluster_release(mapa_u32(lnb, dst));
+            }
+            mbar_wait_cluster_acquire(ln_bar, (uint32_t) par);
+            float mean = 0.f;
+            float2 part[2 * Cfg::kLnMaxPairs];
+            const int nparts = 2 * npairs;
+#pragma unroll
+            for (int k = 0; k < 2 * Cfg::kLnMaxPairs; ++k) {
+                if (k < nparts) {
+                    part[k] = *reinterpret_cast<const float2 *>(smem_lnstat + (((par * Cfg::kLnMaxPairs + (k >> 1)) * 2 + (k & 1)) * BM + row) * 8);
+                    mean += part[k].x;
+                }
+            }
+            mean /= (float) nparts;
+            float M2 = 0.f;
+#pragma unroll
+            for (int k = 0; k < 2 * Cfg::kLnMaxPairs; ++k) {
+                if (k < nparts) { const float dm = part[k].x - mean; M2 += part[k].y + (float) (64 * NBW) * dm * dm; }
+            }
+            const float rstd = 1.0f / sqrtf(M2 / (float) p.N + 1e-5f);
+            const float2 nmean = make_float2(-mean, -mean), rstd2 = make_float2(rstd, rstd);
+            // ---- pass 2: normalise out of registers, store out (st) and its fake-quantised twin (rs)
+#pragma unroll
+            for (int bi = 0; bi < NBW; ++bi) {
+                const int b = half + 2 * bi;
+                const int c0 = nb * BN + b * 64;
+                if (lane == 0) tma_store_wait_read<0>();       // previous stores are done with st / rs
+                __syncwarp();
+#pragma unroll
+                for (int hh = 0; hh < 2; ++hh) {
+                    float2 v[16];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const float4 g = *reinterpret_cast<const float4 *>(s_gamma + b * 64 + hh * 32 + 4 * i);
+                        const float4 be = *reinterpret_cast<const float4 *>(s_beta + b * 64 + hh * 32 + 4 * i);
+                        const float2 x0 = __half22float2(*reinterpret_cast<const __half2 *>(&hv[bi][hh * 16 + 2 * i]));
+                        const float2 x1 = __half22float2(*reinterpret_cast<const __half2 *>(&hv[bi][hh * 16 + 2 * i + 1]));
+                        const float2 n0 = __fmul2_rn(__fadd2_rn(x0, nmean), rstd2), n1 = __fmul2_rn(__fadd2_rn(x1, nmean), rstd2);
+                        v[2 * i] = __ffma2_rn(n0, make_float2(g.x, g.y), make_float2(be.x, be.y));
+                        v[2 * i + 1] = __ffma2_rn(n1, make_float2(g.z, g.w), make_float2(be.z, be.w));
+                    }
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int c = hh * 4 + i;
+                        uint4 u;
+                        __half2 * h = reinterpret_cast<__half2 *>(&u);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) h[k] = __floats2half2_rn(v[i * 4 + k].x, v[i * 4 + k].y);
+                        *reinterpret_cast<uint4 *>(st + lane * 128 + ((c ^ (lane & 7)) << 4)) = u;
+                    }
+                    if (fq_on) {
+                        fake_quant32_v2(v, p.fq_type);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const int c = hh * 4 + i;
+                            uint4 u;
+                            __half2 * h = reinterpret_cast<__half2 *>(&u);
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) h[k] = __floats2half2_rn(v[i * 4 + k].x, v[i * 4 + k].y);
+                            *reinterpret_cast<uint4 *>(rs + lane * 128 + ((c ^ (lane & 7)) << 4)) = u;
+                        }
+                    }
+                }
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                    tma_store_2d(&tmap_out, st, c0, wrow0);
+                    if (fq_on) tma_store_2d(&tmap_out2, rs, c0, wrow0);
+                    tma_store_commit();
+                }
+            }
+            // rs doubles as the twin's staging buffer: the next tile's residual may only land once the
+            // last store has finished reading it
+            if (it + 1 < my_tiles && lane == 0) { tma_store_wait_read<0>(); res_load(it + 1); }
+        }
+        if (lane == 0) tma_store_wait_all<0>();
+      } else {
         // ------------------------------------------------------------ epilogue (8 warps per CTA)
         // Two warps per TMEM lane quadrant take alternate 64-column boxes of the tile, so every
         // scheduler has two epilogue warps to interleave.  Per box: TMEM -> registers ; bias (from a
@@ -298,15 +515,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         uint8_t * rs = smem_res + e * 4096;
         float * bslot = reinterpret_cast<float *>(smem_bias + e * 256);
         uint64_t * rbar = rfull + e;
-        const uint32_t tempty_leader = mapa_u32(smem_u32(&tempty[0]), 0);
+        const uint32_t tempty_leader = mapa_u32(smem_u32(&tempty[0]), leader);
         const bool has_res = (p.epilogue & EPI_RESIDUAL) != 0;
         const bool has_bias = (p.epilogue & EPI_BIAS) != 0;
         const int total_boxes = my_tiles * nbw;
         auto box_coords = [&](int j, int & c0, int & row0, int & b) {
-            const int tile = tw.tile(j / nbw);
+            int mb, nb; tw.get(j / nbw, mb, nb);
             b = half + 2 * (j % nbw);
-            c0 = (tile % tw.num_n) * BN + b * 64;
-            row0 = (tile / tw.num_n) * (2 * BM) + (int) rank * BM + q * 32;
+            c0 = nb * BN + b * 64;
+            row0 = mb * (2 * BM) + (int) rank * BM + q * 32;
         };
         float2 bnext = make_float2(0.f, 0.f);
         if (total_boxes > 0) {
@@ -401,8 +618,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             if (lane == 0) mbar_arrive_cluster(tempty_leader + 8 * acc);
         }
         if (lane == 0) tma_store_wait_all<0>();
+      }
     } else {
-      if constexpr (Q4) reg_dealloc<kRegsDequant>();
+      if constexpr (Q4) reg_dealloc<RegBudget<LN>::kDequant>();
         // ------------------------------------------------------------ q4 dequant (both CTAs)
         // Each CTA dequantises the BN/2 weight rows it contributes to the pair's B operand, reading
         // the 4-bit stage from the smem ring the bulk-copy warp fills (no global loads here, so the
@@ -413,7 +631,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             constexpr int UNITS = (NUNIT + GT - 1) / GT;         // per thread
             const int grp = (warp - CTRL_WARPS - EPI_WARPS) / DQ_GROUP_WARPS;
             const int tg = threadIdx.x - 32 * (CTRL_WARPS + EPI_WARPS) - grp * GT;         // 0..GT-1
-            const uint32_t bfull_leader = mapa_u32(smem_u32(&b_full[0]), 0);
+            const uint32_t bfull_leader = mapa_u32(smem_u32(&b_full[0]), leader);
             const int total = my_tiles * num_k;
             int sn = grp % SN, sb = grp % SB;
             uint32_t phn = 0, phb = 0;
@@ -467,49 +685,61 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     if (warp == 1) tmem_dealloc_pair(tmem_base, Cfg::kTmemCols);
 }
 
-// Persistent grid: as many CTA pairs as the device can keep resident (cached per device).
-template <int BN, int WT>
-static int max_clusters(int device, int num_sms) {
-    static int cached[64] = {0};
-    if (device >= 0 && device < 64 && cached[device] > 0) return cached[device];
-    using Cfg = GemmCfg<BN, WT>;
+// Persistent grid: as many clusters as the device can keep resident (cached per device and cluster size).
+template <int BN, int WT, bool LN>
+static int max_clusters(int device, int num_sms, int csize) {
+    static int cached[64][9] = {};
+    if (device >= 0 && device < 64 && cached[device][csize] > 0) return cached[device][csize];
+    using Cfg = GemmCfg<BN, WT, LN>;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned) (num_sms & ~1));
+    cfg.gridDim = dim3((unsigned) (num_sms / csize * csize));
     cfg.blockDim = dim3(gemm_threads<WT>());
     cfg.dynamicSmemBytes = Cfg::kSmemBytes;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    at[0].val.clusterDim.x = (unsigned) csize; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
     int n = 0;
-    if (cudaOccupancyMaxActiveClusters(&n, gemm_tc_kernel<BN, WT>, &cfg) != cudaSuccess || n <= 0) {
+    if (cudaOccupancyMaxActiveClusters(&n, gemm_tc_kernel<BN, WT, LN>, &cfg) != cudaSuccess || n <= 0) {
         cudaGetLastError();
-        n = num_sms / 2;
+        n = csize == 2 ? num_sms / 2 : 1;
     }
-    if (n > num_sms / 2) n = num_sms / 2;
-    if (device >= 0 && device < 64) cached[device] = n;
+    if (n > num_sms / csize) n = num_sms / csize;
+    if (device >= 0 && device < 64) cached[device][csize] = n;
     return n;
 }
 
-template <int BN, int WT>
+template <int BN, int WT, bool LN>
 static cudaError_t launch_one(const GemmArgs & g, int num_sms, cudaStream_t st) {
-    using Cfg = GemmCfg<BN, WT>;
+    using Cfg = GemmCfg<BN, WT, LN>;
     static_assert(Cfg::kSA >= 3, "pipeline too shallow");
-    auto kern = gemm_tc_kernel<BN, WT>;
+    auto kern = gemm_tc_kernel<BN, WT, LN>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
     if (e != cudaSuccess) return e;
     int device = 0;
     cudaGetDevice(&device);
     const DevWeight & w = *g.w;
-    GemmParams p{w.qnib, w.qd, w.qm, w.bias, g.out, g.M, w.N, w.K, g.epilogue, g.fq_type};
-    const int tiles = ((g.M + 2 * BM - 1) / (2 * BM)) * (w.N / BN);
-    const int ncl_max = max_clusters<BN, WT>(device, num_sms);
-    const int ncl = tiles < ncl_max ? tiles : ncl_max;
+    GemmParams p{w.qnib, w.qd, w.qm, w.bias, g.out, g.ln_gamma, g.ln_beta, g.M, w.N, w.K, g.epilogue, g.fq_type};
+    const int num_m = (g.M + 2 * BM - 1) / (2 * BM), num_n = w.N / BN;
+    const int csize = LN ? 2 * num_n : 2;                 // CTAs per cluster
+    const int units = LN ? num_m : num_m * num_n;         // stripes or tiles to hand out
+    const int ncl_max = max_clusters<BN, WT, LN>(device, num_sms, csize);
+    const int ncl = units < ncl_max ? units : ncl_max;
     if (ncl <= 0) return cudaSuccess;
     if ((g.epilogue & EPI_RESIDUAL) && !g.tmap_res) return cudaErrorInvalidValue;
+    if (LN && (!g.ln_gamma || !g.ln_beta || !g.tmap_res || !w.bias || ((g.epilogue & EPI_FAKEQUANT) && !g.tmap_out2))) return cudaErrorInvalidValue;
     const CUtensorMap * tres = g.tmap_res ? g.tmap_res : g.tmap_out;
-    kern<<<2 * ncl, gemm_threads<WT>(), Cfg::kSmemBytes, st>>>(*g.tmap_a, w.tmap, *g.tmap_out, *tres, p);
-    return cudaGetLastError();
+    const CUtensorMap * tout2 = g.tmap_out2 ? g.tmap_out2 : g.tmap_out;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned) (csize * ncl));
+    cfg.blockDim = dim3(gemm_threads<WT>());
+    cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = (unsigned) csize; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, *g.tmap_a, w.tmap, *g.tmap_out, *tres, *tout2, p);
 }
 
 int gemm_pick_bn(int N) {
@@ -520,15 +750,32 @@ int gemm_pick_bn(int N) {
     return 0;
 }
 
+bool gemm_ln_fusable(const DevWeight & w) {
+    // the cluster must hold every column block of a row stripe: N / BN pairs, at most 3 (6 CTAs)
+    return (w.bn == 256 || w.bn == 128) && w.N / w.bn <= 3 && w.bias != nullptr;
+}
+
 cudaError_t launch_gemm_tc(const GemmArgs & g, int num_sms, cudaStream_t st) {
     const DevWeight & w = *g.w;
     const int bn = w.bn;
     if (bn == 0 || w.K % BK != 0) return cudaErrorInvalidValue;
+    if (g.epilogue & EPI_LN) {
+        if (!gemm_ln_fusable(w) || (g.epilogue & EPI_GELU) || !(g.epilogue & EPI_RESIDUAL) || !(g.epilogue & EPI_BIAS)) return cudaErrorInvalidValue;
+#define DISPATCH_LN(BN_)                                                                        \
+        switch (w.type) {                                                                       \
+            case W_F16:  return launch_one<BN_, W_F16, true>(g, num_sms, st);                    \
+            case W_Q4_0: return launch_one<BN_, W_Q4_0, true>(g, num_sms, st);                   \
+            case W_Q4_1: return launch_one<BN_, W_Q4_1, true>(g, num_sms, st);                   \
+            default: return cudaErrorInvalidValue;                                              \
+        }
+        if (bn == 256) { DISPATCH_LN(256) } else { DISPATCH_LN(128) }
+#undef DISPATCH_LN
+    }
 #define DISPATCH_WT(BN_)                                                                        \
     switch (w.type) {                                                                           \
-        case W_F16:  return launch_one<BN_, W_F16>(g, num_sms, st);                              \
-        case W_Q4_0: return launch_one<BN_, W_Q4_0>(g, num_sms, st);                             \
-        case W_Q4_1: return launch_one<BN_, W_Q4_1>(g, num_sms, st);                             \
+        case W_F16:  return launch_one<BN_, W_F16, false>(g, num_sms, st);                       \
+        case W_Q4_0: return launch_one<BN_, W_Q4_0, false>(g, num_sms, st);                      \
+        case W_Q4_1: return launch_one<BN_, W_Q4_1, false>(g, num_sms, st);                      \
         default: return cudaErrorInvalidValue;                                                  \
     }
     switch (bn) {

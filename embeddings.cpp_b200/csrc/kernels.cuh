@@ -12,7 +12,7 @@ namespace b200 {
 enum WType : int { W_F32 = 0, W_F16 = 1, W_Q4_0 = 2, W_Q4_1 = 3 };
 
 // epilogue flags of the GEMM
-enum : int { EPI_BIAS = 1, EPI_GELU = 2, EPI_RESIDUAL = 4, EPI_FAKEQUANT = 8 };
+enum : int { EPI_BIAS = 1, EPI_GELU = 2, EPI_RESIDUAL = 4, EPI_FAKEQUANT = 8, EPI_LN = 16 };
 
 // A dense weight matrix W[N][K] (K contiguous = the file's ne0, reference bert.cpp:611-623)
 // resident in HBM in its GEMM-ready form:
@@ -46,10 +46,16 @@ struct GemmArgs {
     int M;                          // valid rows
     int epilogue;                   // EPI_* flags
     int fq_type;                    // W_Q4_0 -> q8_0 rule, W_Q4_1 -> q8_1 rule (EPI_FAKEQUANT)
+    // EPI_LN (with EPI_BIAS | EPI_RESIDUAL): out = LayerNorm(acc + bias + residual) * gamma + beta; with
+    // EPI_FAKEQUANT the q8 fake-quantised twin goes through tmap_out2.  See gemm_ln_fusable().
+    const CUtensorMap * tmap_out2 = nullptr;
+    const float * ln_gamma = nullptr;
+    const float * ln_beta = nullptr;
 };
 
 int gemm_pick_bn(int N);              // N-tile (256/192/128/64) used for a weight with N rows
 cudaError_t launch_gemm_tc(const GemmArgs & g, int num_sms, cudaStream_t st);
+bool gemm_ln_fusable(const DevWeight & w);   // can the LayerNorm after this GEMM run in its epilogue?
 cudaError_t launch_gemm_simt(const GemmArgs & g, cudaStream_t st);      // validation kernel
 
 // Embedding table as stored for the gather kernel (K0).

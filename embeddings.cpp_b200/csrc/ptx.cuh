@@ -5,6 +5,7 @@
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 
 namespace b200 {
 
@@ -53,6 +54,10 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t * bar, uint32_t parity) {
 __device__ __forceinline__ void mbar_wait(uint64_t * bar, uint32_t parity) {
     uint32_t spins = 0;
     while (!mbar_try_wait(bar, parity)) {
+#ifdef BERT_DEBUG_WAIT
+        if (spins == (1u << 22) && (threadIdx.x & 31) == 0)
+            printf("mbar_wait stuck: bar 0x%x parity %u block %d warp %d\n", smem_u32(bar) & 0xFFFFF, parity, (int) blockIdx.x, (int) (threadIdx.x >> 5));
+#endif
         if (++spins > (1u << 26)) { asm volatile("trap;"); }
     }
 }
@@ -180,6 +185,29 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t local, uint32_t rank) {
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
     asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" :: "r"(cluster_addr) : "memory");
 }
+// cluster-scope variants for data exchanged through distributed shared memory
+__device__ __forceinline__ void mbar_arrive_cluster_release(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" :: "r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster_acquire(uint64_t * bar, uint32_t parity) {
+    uint32_t spins = 0, ok = 0;
+    while (true) {
+        asm volatile(
+            "{\n\t.reg .pred P;\n\t"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, P;\n\t}\n"
+            : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+        if (ok) break;
+#ifdef BERT_DEBUG_WAIT
+        if (spins == (1u << 22) && (threadIdx.x & 31) == 0)
+            printf("mbar_wait(cluster) stuck: bar 0x%x parity %u block %d warp %d\n", smem_u32(bar) & 0xFFFFF, parity, (int) blockIdx.x, (int) (threadIdx.x >> 5));
+#endif
+        if (++spins > (1u << 26)) { asm volatile("trap;"); }
+    }
+}
+__device__ __forceinline__ void st_cluster_f32x2(uint32_t cluster_addr, float a, float b) {
+    asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" :: "r"(cluster_addr), "f"(a), "f"(b) : "memory");
+}
 // CTA-pair TMA load: data lands in THIS CTA's smem, the transaction bytes are signalled on an
 // mbarrier given by its shared::cluster address (the leader CTA's barrier)
 __device__ __forceinline__ void tma_load_2d_pair(void * smem_dst, const void * tmap, uint32_t bar_cluster_addr,
@@ -210,10 +238,11 @@ __device__ __forceinline__ void umma_f16_ss_pair(uint32_t d_tmem, uint64_t a_des
         "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}\n"
         :: "r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
 }
-// when all previously issued MMAs complete, arrive on the mbarrier at this smem offset in BOTH CTAs
-__device__ __forceinline__ void umma_commit_pair(uint64_t * bar) {
+// when all previously issued MMAs complete, arrive on the mbarrier at this smem offset in BOTH CTAs of
+// the pair (cta_mask = 3 << rank of the pair's even CTA in the cluster)
+__device__ __forceinline__ void umma_commit_pair(uint64_t * bar, uint16_t cta_mask) {
     asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-                 :: "r"(smem_u32(bar)), "h"((uint16_t) 3) : "memory");
+                 :: "r"(smem_u32(bar)), "h"(cta_mask) : "memory");
 }
 
 // ---------------------------------------------------------------- UMMA descriptors

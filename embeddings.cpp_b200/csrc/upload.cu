@@ -107,8 +107,8 @@ __device__ __forceinline__ float gelu_ref_numerics_v(float x) {
 __global__ void gemm_simt_kernel(const __half * __restrict__ a, const DevWeight w,
                                  const __half * __restrict__ residual, __half * __restrict__ out,
                                  int M, int epilogue, int fq_type) {
-    const int row = blockIdx.y;
-    const int cb = blockIdx.x * blockDim.x + threadIdx.x;        // 32-column block
+    const int row = blockIdx.x;                                  // rows on x: M may exceed the 65535 limit of y
+    const int cb = blockIdx.y * blockDim.x + threadIdx.x;        // 32-column block
     if (row >= M || cb >= w.N / 32) return;
     float v[32];
     for (int j = 0; j < 32; ++j) v[j] = 0.f;
@@ -201,7 +201,7 @@ cudaError_t launch_dequant_q4_f32(const DevWeight & w, float * out, cudaStream_t
 cudaError_t launch_gemm_simt(const GemmArgs & g, cudaStream_t st) {
     if (g.M <= 0) return cudaSuccess;
     const DevWeight & w = *g.w;
-    dim3 grid((w.N / 32 + 63) / 64, g.M);
+    dim3 grid(g.M, (w.N / 32 + 63) / 64);
     gemm_simt_kernel<<<grid, 64, 0, st>>>(g.a, w, g.residual, g.out, g.M, g.epilogue, g.fq_type);
     return cudaGetLastError();
 }

@@ -60,6 +60,19 @@ def test_tcgen05_gemm_with_q8_fakequant_epilogue(pkg, wt, M, N, K, epi):
     assert np.isfinite(err) and err <= 1.1 * ref / 127 + 4e-3 * ref, (err, ref)
 
 
+# EPI_LN = 16: LayerNorm of (acc + bias + residual) inside the GEMM epilogue, statistics exchanged between the
+# CTAs of a cluster through DSMEM; checked against validation GEMM + the stand-alone LayerNorm row kernel
+@pytest.mark.parametrize("wt,M,N,K,epi", [
+    (1, 600, 768, 768, 21), (2, 1000, 768, 768, 29), (3, 777, 768, 3072, 29), (2, 515, 512, 1536, 29),
+    (2, 300, 256, 256, 21), (1, 131, 128, 512, 29), (2, 70000, 768, 768, 29),
+])
+def test_tcgen05_gemm_with_fused_layernorm_epilogue(pkg, wt, M, N, K, epi):
+    rc, err, ref = pkg.selftest_gemm(M, N, K, wt, epi, seed=5)
+    assert rc == 0
+    tol = 4e-3 * max(ref, 1.0) + (1.1 * ref / 127 if epi & 8 else 0.0)
+    assert np.isfinite(err) and err <= tol, (err, ref)
+
+
 @pytest.mark.parametrize("n_sent,L,nh,d", [(5, 64, 2, 64), (7, 200, 4, 64), (3, 512, 12, 64), (9, 130, 12, 32),
                                            (4, 512, 2, 32), (33, 17, 12, 64), (1, 1, 2, 32), (2, 2, 2, 64)])
 def test_fused_attention_matches_reference_kernel(pkg, n_sent, L, nh, d):
