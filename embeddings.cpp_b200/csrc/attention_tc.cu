@@ -90,7 +90,9 @@ __global__ void __launch_bounds__(ATT_TC_THREADS, 2)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv,
                     const AttnTcParams p) {
     extern __shared__ uint8_t smem_raw[];
-    uint8_t * smem = (uint8_t *) (((uintptr_t) smem_raw + 1023) & ~(uintptr_t) 1023);
+    // 1024-B alignment by an offset from the array (not an integer round trip), so that the compiler keeps the
+    // shared address space and emits LDS/STS rather than generic LD/ST
+    uint8_t * smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t * smem_q = smem;
     uint8_t * smem_k = smem + kQBytes;                               // KV_STAGES x 8 KB
     uint8_t * smem_v = smem_k + KV_STAGES * kKVBytes;                // KV_STAGES x 8 KB

@@ -161,7 +161,10 @@ constexpr int DQ_GROUP_WARPS = DQ_WARPS / DQ_GROUPS;
 constexpr int CTRL_WARPS = 4;
 template <int WT> constexpr int gemm_threads() { return 32 * (CTRL_WARPS + EPI_WARPS + (WT == W_F16 ? 0 : DQ_WARPS)); }
 constexpr int kRegsCtrl = 40;                                            // q4: 640 threads launch with 96
+// register pool (q4: 640 threads launch with 96): setmaxnreg.inc can only draw on what the CTA's own warps gave
+// back -- control 128 x 56 + dequant 256 x 40 = 17408 -> the 256 epilogue threads may grow by 68, i.e. to 160
 template <bool LN> struct RegBudget { static constexpr int kDequant = 56, kEpilogue = 160; };
+static_assert(128 * (96 - kRegsCtrl) + 256 * (96 - RegBudget<false>::kDequant) >= 256 * (RegBudget<false>::kEpilogue - 96), "setmaxnreg pool");
 
 // Launched with a runtime cluster dimension: 2 (one CTA pair) or, with fused LayerNorm, 2 * N / BN.
 template <int BN, int WT, bool LN>
@@ -174,7 +177,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     constexpr int SA = Cfg::kSA, SB = Cfg::kSB, SN = Cfg::kSN;
     constexpr int NB = BN / 64;                               // 64-column output boxes per tile
     extern __shared__ uint8_t smem_raw[];
-    uint8_t * smem = (uint8_t *) (((uintptr_t) smem_raw + 1023) & ~(uintptr_t) 1023);
+    // 1024-B alignment by an offset from the array (not an integer round trip), so that the compiler keeps the
+    // shared address space and emits LDS/STS rather than generic LD/ST
+    uint8_t * smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t * smem_a = smem;                                  // SA x 16 KB
     uint8_t * smem_b = smem_a + SA * Cfg::kABytes;            // SB x (BN/2)*128 B
     uint8_t * smem_out = smem_b + SB * Cfg::kBBytes;          // 8 warps x 4 KB staging for TMA stores
