@@ -23,7 +23,8 @@ constexpr int BK = 64;
 constexpr int UMMA_K = 16;
 constexpr int kSmemLimit = 232448;                   // 227 KB opt-in limit per CTA
 
-template <int BN, int WT, bool LN> struct GemmCfg {
+// RES: the epilogue adds a residual (LN implies RES); without it the residual staging goes to the B ring
+template <int BN, int WT, bool LN, bool RES> struct GemmCfg {
     static constexpr bool kQ4      = WT != W_F16;
     static constexpr int kBHalf    = BN / 2;                 // B rows this CTA supplies
     static constexpr int kABytes   = BM * BK * 2;
@@ -34,7 +35,7 @@ template <int BN, int WT, bool LN> struct GemmCfg {
     static constexpr int kTmemCols = (2 * BN <= 128) ? 128 : (2 * BN <= 256 ? 256 : 512);
     static constexpr int kAccStride = BN <= 64 ? 64 : (BN <= 128 ? 128 : 256);
     static constexpr int kOutBytes = 8 * 4096;          // 8 epilogue warps x [32 rows][128 B] staging for TMA stores
-    static constexpr int kResBytes = 8 * 4096;          // same geometry, residual boxes prefetched by TMA
+    static constexpr int kResBytes = RES ? 8 * 4096 : 0; // same geometry, residual boxes prefetched by TMA
     static constexpr int kBiasBytes = LN ? 0 : 8 * 256; // per warp: the 64 bias values of its current box
     // fused LayerNorm: per-row partial statistics of up to 3 pairs x 2 warps, double-buffered, plus the
     // CTA's 256-column slices of bias / gamma / beta
@@ -47,7 +48,7 @@ template <int BN, int WT, bool LN> struct GemmCfg {
     // the dequantised B only a short ring (it is produced from smem), the 4-bit ring hides L2 latency.
     static constexpr int kFitF16   = (kSmemLimit - kFixed) / (kABytes + kBBytes);
     static constexpr int kSA       = kQ4 ? (LN ? 4 : 5) : (kFitF16 > 6 ? 6 : kFitF16);
-    static constexpr int kSB       = kQ4 ? 3 : kSA;
+    static constexpr int kSB       = kQ4 ? (RES ? 3 : (BN > 192 ? 5 : 6)) : kSA;
     // (the 4-bit ring depth stays a multiple of the number of dequant groups, so a slot is always
     // refilled for the same group that drained it)
     static constexpr int kSN       = kQ4 ? 6 : 0;
@@ -167,12 +168,13 @@ template <bool LN> struct RegBudget { static constexpr int kDequant = 56, kEpilo
 static_assert(128 * (96 - kRegsCtrl) + 256 * (96 - RegBudget<false>::kDequant) >= 256 * (RegBudget<false>::kEpilogue - 96), "setmaxnreg pool");
 
 // Launched with a runtime cluster dimension: 2 (one CTA pair) or, with fused LayerNorm, 2 * N / BN.
-template <int BN, int WT, bool LN>
+template <int BN, int WT, bool LN, bool RES>
 __global__ void __launch_bounds__(gemm_threads<WT>(), 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
                const __grid_constant__ CUtensorMap tmap_out2, const GemmParams p) {
-    using Cfg = GemmCfg<BN, WT, LN>;
+    static_assert(RES || !LN, "fused LayerNorm needs the residual path");
+    using Cfg = GemmCfg<BN, WT, LN, RES>;
     constexpr bool Q4 = Cfg::kQ4;
     constexpr int SA = Cfg::kSA, SB = Cfg::kSB, SN = Cfg::kSN;
     constexpr int NB = BN / 64;                               // 64-column output boxes per tile
@@ -220,7 +222,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         tma_prefetch_desc(&tmap_a);
         if (!Q4) tma_prefetch_desc(&tmap_b);
         tma_prefetch_desc(&tmap_out);
-        if (p.epilogue & EPI_RESIDUAL) tma_prefetch_desc(&tmap_res);
+        if (RES) tma_prefetch_desc(&tmap_res);
         for (int s = 0; s < SA; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
         if (Q4) {
             for (int s = 0; s < SB; ++s) { mbar_init(&b_full[s], 2 * DQ_GROUP_WARPS); mbar_init(&b_empty[s], 1); }
@@ -521,7 +523,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         float * bslot = reinterpret_cast<float *>(smem_bias + e * 256);
         uint64_t * rbar = rfull + e;
         const uint32_t tempty_leader = mapa_u32(smem_u32(&tempty[0]), leader);
-        const bool has_res = (p.epilogue & EPI_RESIDUAL) != 0;
+        const bool has_res = RES;
         const bool has_bias = (p.epilogue & EPI_BIAS) != 0;
         const int total_boxes = my_tiles * nbw;
         auto box_coords = [&](int j, int & c0, int & row0, int & b) {
@@ -691,11 +693,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 }
 
 // Persistent grid: as many clusters as the device can keep resident (cached per device and cluster size).
-template <int BN, int WT, bool LN>
+template <int BN, int WT, bool LN, bool RES>
 static int max_clusters(int device, int num_sms, int csize) {
     static int cached[64][9] = {};
     if (device >= 0 && device < 64 && cached[device][csize] > 0) return cached[device][csize];
-    using Cfg = GemmCfg<BN, WT, LN>;
+    using Cfg = GemmCfg<BN, WT, LN, RES>;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned) (num_sms / csize * csize));
     cfg.blockDim = dim3(gemm_threads<WT>());
@@ -705,7 +707,7 @@ static int max_clusters(int device, int num_sms, int csize) {
     at[0].val.clusterDim.x = (unsigned) csize; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
     int n = 0;
-    if (cudaOccupancyMaxActiveClusters(&n, gemm_tc_kernel<BN, WT, LN>, &cfg) != cudaSuccess || n <= 0) {
+    if (cudaOccupancyMaxActiveClusters(&n, gemm_tc_kernel<BN, WT, LN, RES>, &cfg) != cudaSuccess || n <= 0) {
         cudaGetLastError();
         n = csize == 2 ? num_sms / 2 : 1;
     }
@@ -714,11 +716,11 @@ static int max_clusters(int device, int num_sms, int csize) {
     return n;
 }
 
-template <int BN, int WT, bool LN>
+template <int BN, int WT, bool LN, bool RES>
 static cudaError_t launch_one(const GemmArgs & g, int num_sms, cudaStream_t st) {
-    using Cfg = GemmCfg<BN, WT, LN>;
+    using Cfg = GemmCfg<BN, WT, LN, RES>;
     static_assert(Cfg::kSA >= 3, "pipeline too shallow");
-    auto kern = gemm_tc_kernel<BN, WT, LN>;
+    auto kern = gemm_tc_kernel<BN, WT, LN, RES>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
     if (e != cudaSuccess) return e;
     int device = 0;
@@ -728,7 +730,7 @@ static cudaError_t launch_one(const GemmArgs & g, int num_sms, cudaStream_t st) 
     const int num_m = (g.M + 2 * BM - 1) / (2 * BM), num_n = w.N / BN;
     const int csize = LN ? 2 * num_n : 2;                 // CTAs per cluster
     const int units = LN ? num_m : num_m * num_n;         // stripes or tiles to hand out
-    const int ncl_max = max_clusters<BN, WT, LN>(device, num_sms, csize);
+    const int ncl_max = max_clusters<BN, WT, LN, RES>(device, num_sms, csize);
     const int ncl = units < ncl_max ? units : ncl_max;
     if (ncl <= 0) return cudaSuccess;
     if ((g.epilogue & EPI_RESIDUAL) && !g.tmap_res) return cudaErrorInvalidValue;
@@ -768,19 +770,27 @@ cudaError_t launch_gemm_tc(const GemmArgs & g, int num_sms, cudaStream_t st) {
         if (!gemm_ln_fusable(w) || (g.epilogue & EPI_GELU) || !(g.epilogue & EPI_RESIDUAL) || !(g.epilogue & EPI_BIAS)) return cudaErrorInvalidValue;
 #define DISPATCH_LN(BN_)                                                                        \
         switch (w.type) {                                                                       \
-            case W_F16:  return launch_one<BN_, W_F16, true>(g, num_sms, st);                    \
-            case W_Q4_0: return launch_one<BN_, W_Q4_0, true>(g, num_sms, st);                   \
-            case W_Q4_1: return launch_one<BN_, W_Q4_1, true>(g, num_sms, st);                   \
+            case W_F16:  return launch_one<BN_, W_F16, true, true>(g, num_sms, st);              \
+            case W_Q4_0: return launch_one<BN_, W_Q4_0, true, true>(g, num_sms, st);             \
+            case W_Q4_1: return launch_one<BN_, W_Q4_1, true, true>(g, num_sms, st);             \
             default: return cudaErrorInvalidValue;                                              \
         }
         if (bn == 256) { DISPATCH_LN(256) } else { DISPATCH_LN(128) }
 #undef DISPATCH_LN
     }
 #define DISPATCH_WT(BN_)                                                                        \
+    if (g.epilogue & EPI_RESIDUAL) {                                                            \
+        switch (w.type) {                                                                       \
+            case W_F16:  return launch_one<BN_, W_F16, false, true>(g, num_sms, st);             \
+            case W_Q4_0: return launch_one<BN_, W_Q4_0, false, true>(g, num_sms, st);            \
+            case W_Q4_1: return launch_one<BN_, W_Q4_1, false, true>(g, num_sms, st);            \
+            default: return cudaErrorInvalidValue;                                              \
+        }                                                                                       \
+    }                                                                                           \
     switch (w.type) {                                                                           \
-        case W_F16:  return launch_one<BN_, W_F16, false>(g, num_sms, st);                       \
-        case W_Q4_0: return launch_one<BN_, W_Q4_0, false>(g, num_sms, st);                      \
-        case W_Q4_1: return launch_one<BN_, W_Q4_1, false>(g, num_sms, st);                      \
+        case W_F16:  return launch_one<BN_, W_F16, false, false>(g, num_sms, st);                \
+        case W_Q4_0: return launch_one<BN_, W_Q4_0, false, false>(g, num_sms, st);               \
+        case W_Q4_1: return launch_one<BN_, W_Q4_1, false, false>(g, num_sms, st);               \
         default: return cudaErrorInvalidValue;                                                  \
     }
     switch (bn) {

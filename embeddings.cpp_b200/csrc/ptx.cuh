@@ -41,13 +41,16 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t * bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint64_t * bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory");
 }
+// try_wait suspends the thread until the phase completes or the time hint (ns) runs out, so a waiting
+// warp wakes on completion but does not burn issue slots polling in between
+constexpr uint32_t kWaitHintNs = 20000;
 __device__ __forceinline__ bool mbar_try_wait(uint64_t * bar, uint32_t parity) {
     uint32_t ok;
     asm volatile(
         "{\n\t.reg .pred P;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2, %3;\n\t"
         "selp.u32 %0, 1, 0, P;\n\t}\n"
-        : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+        : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity), "r"(kWaitHintNs) : "memory");
     return ok != 0;
 }
 // Bounded wait: a protocol bug becomes a trap (launch error) instead of a hung GPU.
@@ -55,10 +58,10 @@ __device__ __forceinline__ void mbar_wait(uint64_t * bar, uint32_t parity) {
     uint32_t spins = 0;
     while (!mbar_try_wait(bar, parity)) {
 #ifdef BERT_DEBUG_WAIT
-        if (spins == (1u << 22) && (threadIdx.x & 31) == 0)
+        if (spins == (1u << 16) && (threadIdx.x & 31) == 0)
             printf("mbar_wait stuck: bar 0x%x parity %u block %d warp %d\n", smem_u32(bar) & 0xFFFFF, parity, (int) blockIdx.x, (int) (threadIdx.x >> 5));
 #endif
-        if (++spins > (1u << 26)) { asm volatile("trap;"); }
+        if (++spins > (1u << 20)) { asm volatile("trap;"); }
     }
 }
 
@@ -194,15 +197,15 @@ __device__ __forceinline__ void mbar_wait_cluster_acquire(uint64_t * bar, uint32
     while (true) {
         asm volatile(
             "{\n\t.reg .pred P;\n\t"
-            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P, [%1], %2;\n\t"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P, [%1], %2, %3;\n\t"
             "selp.u32 %0, 1, 0, P;\n\t}\n"
-            : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+            : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity), "r"(kWaitHintNs) : "memory");
         if (ok) break;
 #ifdef BERT_DEBUG_WAIT
-        if (spins == (1u << 22) && (threadIdx.x & 31) == 0)
+        if (spins == (1u << 16) && (threadIdx.x & 31) == 0)
             printf("mbar_wait(cluster) stuck: bar 0x%x parity %u block %d warp %d\n", smem_u32(bar) & 0xFFFFF, parity, (int) blockIdx.x, (int) (threadIdx.x >> 5));
 #endif
-        if (++spins > (1u << 26)) { asm volatile("trap;"); }
+        if (++spins > (1u << 20)) { asm volatile("trap;"); }
     }
 }
 __device__ __forceinline__ void st_cluster_f32x2(uint32_t cluster_addr, float a, float b) {
