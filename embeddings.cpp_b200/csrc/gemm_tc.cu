@@ -124,13 +124,18 @@ constexpr int EPI_WARPS = 8;         // epilogue warps (two per TMEM lane quadra
 // The nibble is OR-ed into the mantissa of an fp16 constant whose ulp matches the nibble's
 // bit position (1024 for mantissa bits 0-3, 64 for bits 4-7), so a word needs one shift for its
 // four pairs; then (q - 8) * d  or  q * d + m  in half2.
+__device__ __forceinline__ uint32_t and_or(uint32_t a, uint32_t mask, uint32_t bits) {
+    uint32_t x;                              // (a & mask) | bits in one LOP3
+    asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(x) : "r"(a), "r"(mask), "r"(bits));
+    return x;
+}
 template <int WT>
 __device__ __forceinline__ uint32_t dq_pair(uint32_t w, int i, __half2 d2, __half2 m2) {
     uint32_t x;
     unsigned short base;                 // fp16 bits of (magic + 8) for q4_0, magic for q4_1
     const uint32_t ws = i < 2 ? w : (w >> 8);                       // one shift serves pairs 2 and 3
-    if ((i & 1) == 0) { x = (ws & 0x000F000Fu) | 0x64006400u; base = WT == W_Q4_0 ? 0x6408 : 0x6400; }   // 1024 + q
-    else              { x = (ws & 0x00F000F0u) | 0x54005400u; base = WT == W_Q4_0 ? 0x5480 : 0x5400; }   //   64 + q
+    if ((i & 1) == 0) { x = and_or(ws, 0x000F000Fu, 0x64006400u); base = WT == W_Q4_0 ? 0x6408 : 0x6400; }   // 1024 + q
+    else              { x = and_or(ws, 0x00F000F0u, 0x54005400u); base = WT == W_Q4_0 ? 0x5480 : 0x5400; }   //   64 + q
     __half2 h = __hsub2(*reinterpret_cast<__half2 *>(&x), __half2half2(__ushort_as_half(base)));
     h = WT == W_Q4_0 ? __hmul2(h, d2) : __hfma2(h, d2, m2);
     return *reinterpret_cast<uint32_t *>(&h);
@@ -164,8 +169,10 @@ template <int WT> constexpr int gemm_threads() { return 32 * (CTRL_WARPS + EPI_W
 constexpr int kRegsCtrl = 40;                                            // q4: 640 threads launch with 96
 // register pool (q4: 640 threads launch with 96): setmaxnreg.inc can only draw on what the CTA's own warps gave
 // back -- control 128 x 56 + dequant 256 x 40 = 17408 -> the 256 epilogue threads may grow by 68, i.e. to 160
-template <bool LN> struct RegBudget { static constexpr int kDequant = 56, kEpilogue = 160; };
-static_assert(128 * (96 - kRegsCtrl) + 256 * (96 - RegBudget<false>::kDequant) >= 256 * (RegBudget<false>::kEpilogue - 96), "setmaxnreg pool");
+template <bool LN> struct RegBudget {
+    static constexpr int kDequant = LN ? 56 : 64, kEpilogue = LN ? 160 : 152;
+    static_assert(128 * (96 - kRegsCtrl) + 256 * (96 - kDequant) >= 256 * (kEpilogue - 96), "setmaxnreg pool");
+};
 
 // Launched with a runtime cluster dimension: 2 (one CTA pair) or, with fused LayerNorm, 2 * N / BN.
 template <int BN, int WT, bool LN, bool RES>
@@ -657,24 +664,37 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 }
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&n_empty[sn]);            // slot may be refilled
-                mbar_wait(&b_empty[sb], phb ^ 1);
+                // dequantise into registers first (one 32-weight unit at a time: the register budget of these warps is small):
+                // only the stores of the first batch sit between "slot free" and "slot full"
+                constexpr int UB = 1;
                 uint8_t * bt = smem_b + sb * Cfg::kBBytes;
 #pragma unroll
-                for (int u = 0; u < UNITS; ++u) {
-                    const int unit = tg + GT * u;
-                    if (unit >= NUNIT) continue;
-                    const int r = unit >> 1, half_k = unit & 1;          // row in this CTA's half, which 32-block
-                    const __half2 d2 = __half2half2(d[u]), m2 = __half2half2(m[u]);
-                    const uint32_t w[4] = {nib[u].x, nib[u].y, nib[u].z, nib[u].w};
+                for (int u0 = 0; u0 < UNITS; u0 += UB) {
+                    uint4 o[UB][4];
 #pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        uint4 o;
-                        o.x = dq_pair<WT>(w[c], 0, d2, m2);
-                        o.y = dq_pair<WT>(w[c], 1, d2, m2);
-                        o.z = dq_pair<WT>(w[c], 2, d2, m2);
-                        o.w = dq_pair<WT>(w[c], 3, d2, m2);
-                        const int chunk = half_k * 4 + c;
-                        *reinterpret_cast<uint4 *>(bt + r * 128 + ((chunk ^ (r & 7)) << 4)) = o;
+                    for (int v = 0; v < UB; ++v) {
+                        const int u = u0 + v;
+                        const __half2 d2 = __half2half2(d[u]), m2 = __half2half2(m[u]);
+                        const uint32_t w[4] = {nib[u].x, nib[u].y, nib[u].z, nib[u].w};
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) {
+                            o[v][c].x = dq_pair<WT>(w[c], 0, d2, m2);
+                            o[v][c].y = dq_pair<WT>(w[c], 1, d2, m2);
+                            o[v][c].z = dq_pair<WT>(w[c], 2, d2, m2);
+                            o[v][c].w = dq_pair<WT>(w[c], 3, d2, m2);
+                        }
+                    }
+                    if (u0 == 0) mbar_wait(&b_empty[sb], phb ^ 1);
+#pragma unroll
+                    for (int v = 0; v < UB; ++v) {
+                        const int unit = tg + GT * (u0 + v);
+                        if (unit >= NUNIT) continue;
+                        const int r = unit >> 1, half_k = unit & 1;          // row in this CTA's half, which 32-block
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) {
+                            const int chunk = half_k * 4 + c;
+                            *reinterpret_cast<uint4 *>(bt + r * 128 + ((chunk ^ (r & 7)) << 4)) = o[v][c];
+                        }
                     }
                 }
                 fence_proxy_async_smem();
