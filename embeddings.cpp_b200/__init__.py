@@ -15,7 +15,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libbert.so")
+LIB_PATH = os.environ.get("BERT_B200_LIB") or os.path.join(HERE, "lib", "libbert.so")   # env: A/B runs of two builds (tools/ab.py)
 
 _lib = None
 

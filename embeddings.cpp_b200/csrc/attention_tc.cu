@@ -31,7 +31,9 @@ constexpr int KV_STAGES = 4;
 constexpr int ATT_TC_THREADS = 192;
 constexpr int kQBytes = AQ * AD * 2;          // 16 KB
 constexpr int kKVBytes = AK * AD * 2;         // 8 KB each for K and V
-constexpr int kAttSmem = kQBytes + KV_STAGES * 2 * kKVBytes + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int Q_STAGES = 1;
+constexpr int kOutStage = 4 * 4096;            // per softmax warp: [32 rows][128 B] staging for coalesced output rows
+constexpr int kAttSmem = Q_STAGES * kQBytes + KV_STAGES * 2 * kKVBytes + kOutStage + 1024 /*align*/ + 256 /*barriers*/;
 constexpr uint32_t TM_S = 0;       // S buffers at columns 0 and 64 (P aliases the first 32 columns of each)
 constexpr uint32_t TM_O = 128;     // O accumulator: 64 columns
 constexpr uint32_t TM_COLS = 256;
@@ -44,36 +46,44 @@ struct AttnTcParams {
     float scale_log2;
 };
 
-struct Item { int t0, len, q0, head; __device__ __forceinline__ bool valid() const { return q0 < len; } };
+// t1 (the sentence's end offset) is kept raw: the length is only formed where it is used, so the two
+// global loads of a prefetched item are not waited for at decode time
+struct Item {
+    int t0, t1, q0, head;
+    __device__ __forceinline__ int len() const { return t1 - t0; }
+    __device__ __forceinline__ bool valid() const { return q0 < t1 - t0; }
+};
 
-__device__ __forceinline__ Item decode_item(const AttnTcParams & p, int item, int total) {
-    Item it;
-    if (item >= total) { it.t0 = it.len = it.q0 = it.head = 0; return it; }
-    const int qt = item % p.max_qt;
-    const int hs = item / p.max_qt;
-    it.head = hs % p.n_head;
-    const int sent = hs / p.n_head;
-    it.t0 = __ldg(p.cu + sent);
-    it.len = __ldg(p.cu + sent + 1) - it.t0;
-    it.q0 = qt * AQ;
-    return it;
-}
-
-// Round-robin item walk with the NEXT item's sentence bounds (two dependent-free global loads)
-// fetched while the current item is processed, so their latency is off the critical path.
+// Round-robin item walk (item = (sentence, head, query tile), query tile fastest).  The coordinates of the
+// NEXT item are advanced incrementally (no integer division per item) and its sentence bounds -- two
+// dependent-free global loads -- are fetched while the current item is processed.
 struct ItemWalk {
     int next_item, total, stride;
+    int qt, head, sent;            // coordinates of next_item
+    int dq, dh, ds;                // stride split into (query tiles, heads, sentences)
     Item cur, nxt;
+    __device__ __forceinline__ void fetch(const AttnTcParams & p) {
+        if (next_item >= total) { nxt.t0 = nxt.t1 = nxt.q0 = nxt.head = 0; return; }
+        nxt.head = head;
+        nxt.q0 = qt * AQ;
+        nxt.t0 = __ldg(p.cu + sent);
+        nxt.t1 = __ldg(p.cu + sent + 1);
+    }
     __device__ __forceinline__ ItemWalk(const AttnTcParams & p, int first, int stride_, int total_)
         : next_item(first), total(total_), stride(stride_) {
-        nxt = decode_item(p, next_item, total);
+        qt = first % p.max_qt; const int hs = first / p.max_qt; head = hs % p.n_head; sent = hs / p.n_head;
+        dq = stride % p.max_qt; const int sh = stride / p.max_qt; dh = sh % p.n_head; ds = sh / p.n_head;
+        fetch(p);
     }
     // moves to the next item of this CTA; false when the walk is over
     __device__ __forceinline__ bool advance(const AttnTcParams & p) {
         if (next_item >= total) return false;
         cur = nxt;
         next_item += stride;
-        nxt = decode_item(p, next_item, total);
+        qt += dq; head += dh; sent += ds;
+        if (qt >= p.max_qt) { qt -= p.max_qt; ++head; }
+        if (head >= p.n_head) { head -= p.n_head; ++sent; }
+        fetch(p);
         return true;
     }
 };
@@ -94,17 +104,18 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     // shared address space and emits LDS/STS rather than generic LD/ST
     uint8_t * smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t * smem_q = smem;
-    uint8_t * smem_k = smem + kQBytes;                               // KV_STAGES x 8 KB
+    uint8_t * smem_k = smem + Q_STAGES * kQBytes;                    // KV_STAGES x 8 KB
     uint8_t * smem_v = smem_k + KV_STAGES * kKVBytes;                // KV_STAGES x 8 KB
-    uint64_t * bars = (uint64_t *) (smem_v + KV_STAGES * kKVBytes);
-    uint64_t * q_full = bars;                   // [1]
-    uint64_t * q_empty = bars + 1;              // [1]
-    uint64_t * kv_full = bars + 2;              // [KV_STAGES]
+    uint8_t * smem_o = smem_v + KV_STAGES * kKVBytes;                // 4 x 4 KB output staging
+    uint64_t * bars = (uint64_t *) (smem_o + kOutStage);
+    uint64_t * q_full = bars;                   // [Q_STAGES]
+    uint64_t * q_empty = bars + Q_STAGES;       // [Q_STAGES]
+    uint64_t * kv_full = q_empty + Q_STAGES;    // [KV_STAGES]
     uint64_t * kv_empty = kv_full + KV_STAGES;  // [KV_STAGES]
     uint64_t * s_full = kv_empty + KV_STAGES;   // [2]
     uint64_t * p_ready = s_full + 2;            // [2]
-    uint64_t * pv_done = p_ready + 2;           // [1]
-    uint64_t * o_free = pv_done + 1;            // [1]
+    uint64_t * pv_done = p_ready + 2;           // [2]  P V of block g has reached the accumulator (barrier g & 1)
+    uint64_t * o_free = pv_done + 2;            // [1]
     uint32_t * tmem_slot = (uint32_t *) (o_free + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -113,10 +124,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmap_q);
         tma_prefetch_desc(&tmap_kv);
-        mbar_init(q_full, 1); mbar_init(q_empty, 1);
+        for (int a = 0; a < Q_STAGES; ++a) { mbar_init(&q_full[a], 1); mbar_init(&q_empty[a], 1); }
         for (int s = 0; s < KV_STAGES; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
         for (int a = 0; a < 2; ++a) { mbar_init(&s_full[a], 1); mbar_init(&p_ready[a], 4); }
-        mbar_init(pv_done, 1);
+        mbar_init(&pv_done[0], 1); mbar_init(&pv_done[1], 1);
         mbar_init(o_free, 4);
         fence_mbar_init();
     }
@@ -134,10 +145,12 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
             while (walk.advance(p)) {
                 const Item it = walk.cur;
                 if (!it.valid()) continue;
-                const int nb = (it.len + AK - 1) / AK;
-                mbar_wait(q_empty, (item_n & 1) ^ 1);
-                mbar_expect_tx(q_full, kQBytes);
-                tma_load_2d(smem_q, &tmap_q, q_full, it.head * AD, it.t0 + it.q0);
+                const int len = it.len();
+            const int nb = (len + AK - 1) / AK;
+                const uint32_t qs = item_n % Q_STAGES, qph = (item_n / Q_STAGES) & 1;
+                mbar_wait(&q_empty[qs], qph ^ 1);
+                mbar_expect_tx(&q_full[qs], kQBytes);
+                tma_load_2d(smem_q + qs * kQBytes, &tmap_q, &q_full[qs], it.head * AD, it.t0 + it.q0);
                 for (int b = 0; b < nb; ++b, ++kv_it) {
                     const uint32_t st = kv_it % KV_STAGES, ph = (kv_it / KV_STAGES) & 1;
                     mbar_wait(&kv_empty[st], ph ^ 1);
@@ -157,8 +170,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         while (walk.advance(p)) {
             const Item it = walk.cur;
             if (!it.valid()) continue;
-            const int nb = (it.len + AK - 1) / AK;
-            mbar_wait(q_full, item_n & 1);
+            const int len = it.len();
+            const int nb = (len + AK - 1) / AK;
+            const uint32_t qs = item_n % Q_STAGES;
+            mbar_wait(&q_full[qs], (item_n / Q_STAGES) & 1);
             tc_fence_after_sync();
             for (int b = 0; b <= nb; ++b) {
                 if (b < nb) {
@@ -166,13 +181,13 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                     mbar_wait(&kv_full[st], (gb / KV_STAGES) & 1);
                     tc_fence_after_sync();
                     if (elect_one()) {
-                        const uint64_t adesc = umma_smem_desc_sw128(smem_u32(smem_q));
+                        const uint64_t adesc = umma_smem_desc_sw128(smem_u32(smem_q + qs * kQBytes));
                         const uint64_t bdesc = umma_smem_desc_sw128(smem_u32(smem_k + st * kKVBytes));
                         const uint32_t d_tmem = tmem_base + TM_S + (gb & 1) * 64;
 #pragma unroll
                         for (int k = 0; k < AD / 16; ++k) umma_f16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc_s, k != 0);
                         umma_commit(&s_full[gb & 1]);
-                        if (b == nb - 1) umma_commit(q_empty);          // Q tile may be overwritten
+                        if (b == nb - 1) umma_commit(&q_empty[qs]);     // Q tile may be overwritten
                     }
                     __syncwarp();
                 }
@@ -191,7 +206,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                                         (b > 1 || k > 0) ? 1u : 0u);
                         }
                         umma_commit(&kv_empty[st]);
-                        umma_commit(pv_done);
+                        umma_commit(&pv_done[gp & 1]);
                     }
                     __syncwarp();
                 }
@@ -209,7 +224,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         while (walk.advance(p)) {
             const Item it = walk.cur;
             if (!it.valid()) continue;
-            const int nb = (it.len + AK - 1) / AK;
+            const int len = it.len();
+            const int nb = (len + AK - 1) / AK;
             float m_ref = -INFINITY, l = 0.f;
             for (int b = 0; b < nb; ++b) {
                 const uint32_t gb = g + b;
@@ -223,33 +239,36 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                 float s[64];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) { s[j] = __uint_as_float(r0[j]); s[32 + j] = __uint_as_float(r1[j]); }
-                const int kvalid = it.len - b * AK;           // keys of this block inside the sentence
+                const int kvalid = len - b * AK;           // keys of this block inside the sentence
                 if (kvalid < AK) {
 #pragma unroll
                     for (int j = 0; j < 64; ++j) if (j >= kvalid) s[j] = -INFINITY;
                 }
-                float mx = s[0];
+                float mx4[4] = {s[0], s[1], s[2], s[3]};      // four independent chains (a single one is latency-bound)
 #pragma unroll
-                for (int j = 1; j < 64; ++j) mx = fmaxf(mx, s[j]);
-                mx *= p.scale_log2;
+                for (int j = 4; j < 64; j += 4) {
+                    mx4[0] = fmaxf(mx4[0], s[j]); mx4[1] = fmaxf(mx4[1], s[j + 1]);
+                    mx4[2] = fmaxf(mx4[2], s[j + 2]); mx4[3] = fmaxf(mx4[3], s[j + 3]);
+                }
+                const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * p.scale_log2;
                 // move the reference max only on the first block or when it is exceeded by > 2^8
                 const bool need = mx > m_ref + kRescaleThreshold;       // always true on the first block (m_ref = -inf)
                 float factor = 1.f;
                 if (need) { factor = ex2f(m_ref - mx); m_ref = mx; l *= factor; }
-                if (b >= 1) {
-                    // the previous block's P V must be in the accumulator before it may be rescaled
-                    mbar_wait(pv_done, (gb - 1) & 1);
-                    if (__any_sync(0xffffffffu, need)) {
-                        tc_fence_after_sync();
+                if (b >= 1 && __any_sync(0xffffffffu, need)) {
+                    // rare: the previous block's P V must be in the accumulator before it may be rescaled.
+                    // The wait is only paid here: S_b complete (s_full above) implies P V of block b-2 complete
+                    // (issue order ..., PV_{b-2}, S_b, PV_{b-1}), so barrier (gb-1)&1 is at most one phase behind.
+                    mbar_wait(&pv_done[(gb - 1) & 1], ((gb - 1) >> 1) & 1);
+                    tc_fence_after_sync();
 #pragma unroll 1
-                        for (int hh = 0; hh < 2; ++hh) {          // 32 columns at a time: this path is rare, keep it lean in registers
-                            uint32_t o[32];
-                            tmem_ld_32x32b_x32(lane_base + TM_O + hh * 32, o);
-                            tmem_ld_wait();
+                    for (int hh = 0; hh < 2; ++hh) {          // 32 columns at a time: keep this path lean in registers
+                        uint32_t o[32];
+                        tmem_ld_32x32b_x32(lane_base + TM_O + hh * 32, o);
+                        tmem_ld_wait();
 #pragma unroll
-                            for (int j = 0; j < 32; ++j) o[j] = __float_as_uint(__uint_as_float(o[j]) * factor);
-                            tmem_st_32x32b_x32(lane_base + TM_O + hh * 32, o);
-                        }
+                        for (int j = 0; j < 32; ++j) o[j] = __float_as_uint(__uint_as_float(o[j]) * factor);
+                        tmem_st_32x32b_x32(lane_base + TM_O + hh * 32, o);
                     }
                 }
                 const float2 nm2 = make_float2(-m_ref, -m_ref), sc2 = make_float2(p.scale_log2, p.scale_log2);
@@ -271,7 +290,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
             }
             g += nb;
             // ---- finalize: O / l, optional q8 fake-quant per 32-wide block, fp16 store of valid rows
-            mbar_wait(pv_done, (g - 1) & 1);
+            mbar_wait(&pv_done[(g - 1) & 1], ((g - 1) >> 1) & 1);
             tc_fence_after_sync();
             uint32_t o0[32], o1[32];
             tmem_ld_32x32b_x32(lane_base + TM_O, o0);
@@ -281,27 +300,40 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
             __syncwarp();
             if (lane == 0) mbar_arrive(o_free);
             const float inv = 1.f / l;
-            float v0[32], v1[32];
+            const float2 inv2 = make_float2(inv, inv);
+            const bool fq = p.fq_type == W_Q4_0 || p.fq_type == W_Q4_1;
+            uint8_t * stg = smem_o + q * 4096;                  // this warp's [32 rows][128 B], 16-B chunks XOR-swizzled by row
 #pragma unroll
-            for (int j = 0; j < 32; ++j) { v0[j] = __uint_as_float(o0[j]) * inv; v1[j] = __uint_as_float(o1[j]) * inv; }
-            if (p.fq_type == W_Q4_0 || p.fq_type == W_Q4_1) { fake_quant32(v0, p.fq_type); fake_quant32(v1, p.fq_type); }
-            if (it.q0 + row < it.len) {
-                uint4 * op = reinterpret_cast<uint4 *>(p.out + (size_t) (it.t0 + it.q0 + row) * p.H + it.head * AD);
+            for (int hh = 0; hh < 2; ++hh) {
+                float2 v[16];
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    uint4 u;
-                    u.x = pack_h2(v0[8 * c], v0[8 * c + 1]); u.y = pack_h2(v0[8 * c + 2], v0[8 * c + 3]);
-                    u.z = pack_h2(v0[8 * c + 4], v0[8 * c + 5]); u.w = pack_h2(v0[8 * c + 6], v0[8 * c + 7]);
-                    op[c] = u;
+                for (int j = 0; j < 16; ++j) {
+                    const uint32_t * o = hh == 0 ? o0 : o1;
+                    v[j] = __fmul2_rn(make_float2(__uint_as_float(o[2 * j]), __uint_as_float(o[2 * j + 1])), inv2);
                 }
+                if (fq) fake_quant32_v2(v, p.fq_type);
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
                     uint4 u;
-                    u.x = pack_h2(v1[8 * c], v1[8 * c + 1]); u.y = pack_h2(v1[8 * c + 2], v1[8 * c + 3]);
-                    u.z = pack_h2(v1[8 * c + 4], v1[8 * c + 5]); u.w = pack_h2(v1[8 * c + 6], v1[8 * c + 7]);
-                    op[4 + c] = u;
+                    u.x = pack_h2(v[4 * c].x, v[4 * c].y); u.y = pack_h2(v[4 * c + 1].x, v[4 * c + 1].y);
+                    u.z = pack_h2(v[4 * c + 2].x, v[4 * c + 2].y); u.w = pack_h2(v[4 * c + 3].x, v[4 * c + 3].y);
+                    *reinterpret_cast<uint4 *>(stg + lane * 128 + (((hh * 4 + c) ^ (lane & 7)) << 4)) = u;
                 }
             }
+            __syncwarp();
+            // coalesced copy-out: one instruction covers four whole 128-B rows; rows past the sentence end are skipped
+            {
+                const int rows_valid = len - it.q0 - q * 32;       // of this warp's 32 rows
+                __half * obase = p.out + (size_t) (it.t0 + it.q0 + q * 32) * p.H + it.head * AD;
+                const int ch = lane & 7, r0 = lane >> 3;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int r = r0 + 4 * i;
+                    const uint4 u = *reinterpret_cast<const uint4 *>(stg + r * 128 + ((ch ^ (r & 7)) << 4));
+                    if (r < rows_valid) *reinterpret_cast<uint4 *>(obase + (size_t) r * p.H + ch * 8) = u;
+                }
+            }
+            __syncwarp();                                       // staging is reused by the next item
         }
     }
 

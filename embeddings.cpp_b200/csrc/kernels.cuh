@@ -119,4 +119,22 @@ __device__ __forceinline__ void fake_quant32(float (&v)[32], int fq_type) {
     for (int i = 0; i < 32; ++i) v[i] = rintf(v[i] * id) * dd;
 }
 
+// q8 fake-quant of 32 consecutive values (16 float2) held by one thread; rint via the
+// 1.5*2^23 magic constant (round-half-even, |x| <= 127 here) to stay on the FMA pipe
+__device__ __forceinline__ void fake_quant32_v2(float2 (&v)[16], int fq_type) {
+    float amax = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) amax = fmaxf(amax, fmaxf(fabsf(v[i].x), fabsf(v[i].y)));
+    const float d = amax / 127.f;
+    const float id = amax != 0.f ? 127.f / amax : 0.f;
+    const float dd = fq_type == W_Q4_0 ? __half2float(__float2half_rn(d)) : d;
+    const float2 id2 = make_float2(id, id), dd2 = make_float2(dd, dd);
+    const float2 mg = make_float2(12582912.f, 12582912.f), nmg = make_float2(-12582912.f, -12582912.f);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const float2 r = __fadd2_rn(__ffma2_rn(v[i], id2, mg), nmg);
+        v[i] = __fmul2_rn(r, dd2);
+    }
+}
+
 }  // namespace b200
