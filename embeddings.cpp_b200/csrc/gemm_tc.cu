@@ -54,7 +54,7 @@ template <int BN, int WT, bool LN, bool RES> struct GemmCfg {
     static constexpr int kSN       = kQ4 ? 6 : 0;
     static constexpr int kSmemBytes = kSA * kABytes + kSB * kBBytes + kSN * kNibSlot + kFixed;
     static_assert(kSmemBytes <= kSmemLimit, "shared memory budget");
-    static_assert(2 * kSA + 2 * kSB + 2 * kSN + 13 <= (kBarBytes - 8) / 8, "barrier region");
+    static_assert(2 * kSA + 2 * kSB + 2 * kSN + 14 <= (kBarBytes - 8) / 8, "barrier region");
 };
 
 struct GemmParams {
@@ -190,8 +190,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     uint64_t * tfull = n_empty + SN;            // [2]   per CTA, multicast commit
     uint64_t * tempty = tfull + 2;              // [2]   leader's copy is live: 16 epilogue warps arrive
     uint64_t * rfull = tempty + 2;              // [8] residual box, per epilogue warp
-    uint64_t * ln_bar = rfull + 8;              // [1] LN: partial statistics of all pairs have landed
-    uint32_t * tmem_slot = (uint32_t *) (ln_bar + 1);
+    uint64_t * ln_bar = rfull + 8;              // [2] LN: partial statistics of all pairs have landed (by tile parity)
+    uint32_t * tmem_slot = (uint32_t *) (ln_bar + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t crank = cluster_ctarank();                 // rank in the cluster
@@ -220,7 +220,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         }
         for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 2 * EPI_WARPS); }
         for (int i = 0; i < 8; ++i) mbar_init(&rfull[i], 1);
-        if (LN) mbar_init(ln_bar, (uint32_t) tw.num_n * EPI_WARPS * 32);
+        if (LN) { mbar_init(&ln_bar[0], 1); mbar_init(&ln_bar[1], 1); }
         fence_mbar_init();
     }
     if (warp == 1) { tmem_alloc_pair(tmem_slot, Cfg::kTmemCols); tmem_relinquish_pair(); }
@@ -415,13 +415,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             // slot [parity][pair][half][row] in every CTA of the cluster with my pair rank
             const int par = it & 1;
             const uint32_t slot = smem_u32(smem_lnstat) + (uint32_t) ((((par * Cfg::kLnMaxPairs + tw.pair) * 2 + half) * BM + row) * 8);
-            const uint32_t lnb = smem_u32(ln_bar);
+            // st.async: the 8 bytes are counted on the destination CTA's barrier of this tile parity (no fence, no
+            // arrive; the barrier's single arrival is the destination's own expect_tx below)
+            const uint32_t lnb = smem_u32(&ln_bar[par]);
             for (int pj = 0; pj < npairs; ++pj) {
                 const uint32_t dst = (uint32_t) (2 * pj) + rank;
-                st_cluster_f32x2(mapa_u32(slot, dst), mean_p, M2_p);
-                mbar_arrive_cluster_release(mapa_u32(lnb, dst));
+                st_async_f32x2(mapa_u32(slot, dst), mean_p, M2_p, mapa_u32(lnb, dst));
             }
-            mbar_wait_cluster_acquire(ln_bar, (uint32_t) par);
+            if (e == 0 && lane == 0) mbar_expect_tx(&ln_bar[par], (uint32_t) npairs * EPI_WARPS * 32 * 8);
+            mbar_wait(&ln_bar[par], (uint32_t) (it >> 1) & 1);
             float mean = 0.f;
             float2 part[2 * Cfg::kLnMaxPairs];
             const int nparts = 2 * npairs;

@@ -222,6 +222,12 @@ __device__ __forceinline__ void mbar_wait_cluster_acquire(uint64_t * bar, uint32
         if (++spins > (1u << 20)) { asm volatile("trap;"); }
     }
 }
+// asynchronous 8-byte store into a peer CTA's shared memory; the bytes are counted on an mbarrier of the SAME
+// peer CTA (both operands are shared::cluster addresses), so no fence / arrive is needed on the sender side
+__device__ __forceinline__ void st_async_f32x2(uint32_t cluster_addr, float a, float b, uint32_t cluster_mbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f32 [%0], {%1, %2}, [%3];"
+                 :: "r"(cluster_addr), "f"(a), "f"(b), "r"(cluster_mbar) : "memory");
+}
 __device__ __forceinline__ void st_cluster_f32x2(uint32_t cluster_addr, float a, float b) {
     asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" :: "r"(cluster_addr), "f"(a), "f"(b) : "memory");
 }
