@@ -37,9 +37,9 @@ template <int BN, int WT, bool LN, bool RES> struct GemmCfg {
     static constexpr int kOutBytes = 8 * 4096;          // 8 epilogue warps x [32 rows][128 B] staging for TMA stores
     static constexpr int kResBytes = RES ? 8 * 4096 : 0; // same geometry, residual boxes prefetched by TMA
     static constexpr int kBiasBytes = LN ? 0 : 8 * 256; // per warp: the 64 bias values of its current box
-    // fused LayerNorm: per-row partial statistics of up to 3 pairs x 2 warps, double-buffered, plus the
+    // fused LayerNorm: per-row partial statistics of up to 4 pairs x 2 warps, double-buffered, plus the
     // CTA's 256-column slices of bias / gamma / beta
-    static constexpr int kLnMaxPairs = 3;
+    static constexpr int kLnMaxPairs = 4;              // cluster of at most 8 CTAs (the portable limit)
     static constexpr int kLnStatBytes = LN ? 2 * kLnMaxPairs * 2 * BM * 8 : 0;
     static constexpr int kLnParamBytes = LN ? 3 * BN * 4 : 0;
     static constexpr int kBarBytes = 512;
@@ -178,7 +178,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     uint8_t * smem_res = smem_out + Cfg::kOutBytes;           // 8 warps x 4 KB residual boxes
     uint8_t * smem_bias = smem_res + Cfg::kResBytes;          // 8 warps x 64 floats
     uint8_t * smem_nib = smem_bias + Cfg::kBiasBytes;         // SN x 4-bit weight stages (q4 only)
-    uint8_t * smem_lnstat = smem_nib + SN * Cfg::kNibSlot;    // LN: [2][pairs<=3][2][128] x (mean, M2)
+    uint8_t * smem_lnstat = smem_nib + SN * Cfg::kNibSlot;    // LN: [2][pairs<=4][2][128] x (mean, M2)
     uint8_t * smem_lnpar = smem_lnstat + Cfg::kLnStatBytes;   // LN: bias | gamma | beta of this CTA's BN columns
     uint64_t * bars = (uint64_t *) (smem_lnpar + Cfg::kLnParamBytes);
     uint64_t * a_full = bars;                   // [SA]  leader's copy is live (A of both CTAs; + B for fp16 weights)
@@ -763,8 +763,8 @@ int gemm_pick_bn(int N) {
 }
 
 bool gemm_ln_fusable(const DevWeight & w) {
-    // the cluster must hold every column block of a row stripe: N / BN pairs, at most 3 (6 CTAs)
-    return (w.bn == 256 || w.bn == 128) && w.N / w.bn <= 3 && w.bias != nullptr;
+    // the cluster must hold every column block of a row stripe: N / BN pairs, at most 4 (8 CTAs)
+    return (w.bn == 256 || w.bn == 128) && w.N / w.bn <= 4 && w.bias != nullptr;
 }
 
 cudaError_t launch_gemm_tc(const GemmArgs & g, int num_sms, cudaStream_t st) {

@@ -64,7 +64,7 @@ def test_tcgen05_gemm_with_q8_fakequant_epilogue(pkg, wt, M, N, K, epi):
 # CTAs of a cluster through DSMEM; checked against validation GEMM + the stand-alone LayerNorm row kernel
 @pytest.mark.parametrize("wt,M,N,K,epi", [
     (1, 600, 768, 768, 21), (2, 1000, 768, 768, 29), (3, 777, 768, 3072, 29), (2, 515, 512, 1536, 29),
-    (2, 300, 256, 256, 21), (1, 131, 128, 512, 29), (2, 70000, 768, 768, 29),
+    (2, 300, 256, 256, 21), (1, 131, 128, 512, 29), (2, 70000, 768, 768, 29), (2, 600, 1024, 1024, 29), (1, 300, 1024, 512, 21),
 ])
 def test_tcgen05_gemm_with_fused_layernorm_epilogue(pkg, wt, M, N, K, epi):
     rc, err, ref = pkg.selftest_gemm(M, N, K, wt, epi, seed=5)
