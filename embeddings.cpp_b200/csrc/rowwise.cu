@@ -3,9 +3,9 @@
 //                 get_rows ggml.c:11614-11696, norm ggml.c:10605-10653 with eps 1e-5)
 //   K3 ln         LayerNorm of (GEMM + bias + residual)          (bert.cpp:1047-1056, 1073-1082)
 //   K4 pool_norm  mean over the sentence's tokens + L2 normalise (bert.cpp:1087-1095)
-// One warp owns one row; each lane owns one 32-element block (64 B fp16) so that the q8
-// activation fake-quant (one scale per 32 values, ggml.c:1146-1300 / 1425-1480) is
-// thread-local.  Loads/stores are 16-B vectors, statistics are f32 warp-shuffle reductions.
+// One warp owns one row; lane l owns the 16-B chunks l + 32 i, so every warp access is a whole
+// 512-B line group; the q8 activation fake-quant (one scale per 32 values, ggml.c:1146-1300 /
+// 1425-1480) is a 4-lane shuffle.  Statistics are f32 warp-shuffle reductions.
 #include "kernels.cuh"
 
 namespace b200 {
@@ -20,159 +20,14 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
-__device__ __forceinline__ void load32_h(const __half * p, float (&v)[32]) {
-    const uint4 * q = reinterpret_cast<const uint4 *>(p);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const uint4 u = __ldg(q + i);
-        const __half2 * h = reinterpret_cast<const __half2 *>(&u);
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            const float2 f = __half22float2(h[e]);
-            v[i * 8 + 2 * e] = f.x; v[i * 8 + 2 * e + 1] = f.y;
-        }
-    }
-}
-__device__ __forceinline__ void store32_h(__half * p, const float (&v)[32]) {
-    uint4 * q = reinterpret_cast<uint4 *>(p);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        uint4 u;
-        __half2 * h = reinterpret_cast<__half2 *>(&u);
-#pragma unroll
-        for (int e = 0; e < 4; ++e) h[e] = __floats2half2_rn(v[i * 8 + 2 * e], v[i * 8 + 2 * e + 1]);
-        q[i] = u;
-    }
-}
-__device__ __forceinline__ void load32_f(const float * p, float (&v)[32]) {
-    const float4 * q = reinterpret_cast<const float4 *>(p);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const float4 f = __ldg(q + i);
-        v[4 * i] = f.x; v[4 * i + 1] = f.y; v[4 * i + 2] = f.z; v[4 * i + 3] = f.w;
-    }
-}
-
-// LayerNorm of a row distributed as one 32-block per active lane, then write-out.
-__device__ __forceinline__ void ln_finish(float (&v)[32], bool active, int H, int blk,
-                                          const float * gamma, const float * beta,
-                                          __half * out_row, __half * out_fq_row, int fq_type) {
-    float s = 0.f;
-    if (active) {
-#pragma unroll
-        for (int i = 0; i < 32; ++i) s += v[i];
-    }
-    const float mean = warp_sum(s) / (float) H;
-    float s2 = 0.f;
-    if (active) {
-#pragma unroll
-        for (int i = 0; i < 32; ++i) { v[i] -= mean; s2 += v[i] * v[i]; }
-    }
-    const float var = warp_sum(s2) / (float) H;
-    const float scale = 1.0f / sqrtf(var + 1e-5f);
-    if (!active) return;
-    float g[32], b[32];
-    load32_f(gamma + blk * 32, g);
-    load32_f(beta + blk * 32, b);
-#pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] = v[i] * scale * g[i] + b[i];
-    store32_h(out_row + blk * 32, v);
-    if (out_fq_row) {
-        fake_quant32(v, fq_type);
-        store32_h(out_fq_row + blk * 32, v);
-    }
-}
-
-// decode one 32-weight block of an embedding row (file nibble order: byte j = e[j] | e[j+16] << 4)
-__device__ __forceinline__ void decode_block(const DevTable & tb, size_t row, int blk, float (&v)[32]) {
-    const int nb = tb.H / 32;
-    if (tb.type == W_F32) {
-        load32_f(reinterpret_cast<const float *>(tb.data) + row * tb.H + blk * 32, v);
-    } else if (tb.type == W_F16) {
-        load32_h(reinterpret_cast<const __half *>(tb.data) + row * tb.H + blk * 32, v);
-    } else {
-        const uint4 u = __ldg(reinterpret_cast<const uint4 *>(tb.data) + row * nb + blk);
-        const float d = __half2float(__ldg(tb.qd + row * nb + blk));
-        const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-        if (tb.type == W_Q4_0) {
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                const uint32_t byte = (w[j >> 2] >> (8 * (j & 3))) & 0xFF;
-                v[j] = (float) ((int) (byte & 15) - 8) * d;
-                v[j + 16] = (float) ((int) (byte >> 4) - 8) * d;
-            }
-        } else {
-            const float m = __half2float(__ldg(tb.qm + row * nb + blk));
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                const uint32_t byte = (w[j >> 2] >> (8 * (j & 3))) & 0xFF;
-                v[j] = (float) (byte & 15) * d + m;
-                v[j + 16] = (float) (byte >> 4) * d + m;
-            }
-        }
-    }
-}
-
-__global__ void __launch_bounds__(ROWS_PER_CTA * 32)
-embed_ln_kernel(const DevTable word, const float * __restrict__ postype,
-                const float * __restrict__ gamma, const float * __restrict__ beta,
-                const int32_t * __restrict__ ids, const int32_t * __restrict__ cu, int n_sent, int T, int H,
-                __half * __restrict__ out, __half * __restrict__ out_fq, int fq_type) {
-    const int row = blockIdx.x * ROWS_PER_CTA + (threadIdx.x >> 5);
-    if (row >= T) return;
-    const int lane = threadIdx.x & 31;
-    const bool active = lane < H / 32;
-    float v[32];
-    if (active) {
-        int id = ids[row];
-        if (id < 0 || id >= word.rows) id = 0;              // never read out of the table
-        decode_block(word, (size_t) id, lane, v);
-        float pt[32];
-        // position of this packed token inside its sentence: largest s with cu[s] <= row
-        int lo = 0, hi = n_sent;
-        while (hi - lo > 1) {
-            const int mid = (lo + hi) >> 1;
-            if (__ldg(cu + mid) <= row) lo = mid; else hi = mid;
-        }
-        const int pos = row - __ldg(cu + lo);
-        load32_f(postype + (size_t) pos * H + lane * 32, pt);
-#pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] += pt[i];
-    }
-    ln_finish(v, active, H, lane, gamma, beta, out + (size_t) row * H,
-              out_fq ? out_fq + (size_t) row * H : nullptr, fq_type);
-}
-
-// K3.  Lane l owns the 16-B chunks c = l + 32 i (8 fp16 each) of the row, so every warp-level
-// load/store is one fully coalesced 512-B access; a q8 block (32 values) is 4 adjacent lanes.
+// Row LayerNorm + write-out shared by K0 and K3.  Lane l owns the 16-B chunks c = l + 32 i (8 fp16 each)
+// of the row, so every warp-level load/store is one fully coalesced 512-B access; a q8 block (32 values)
+// is 4 adjacent lanes.  `v` holds the row (0 in chunks past the row end), `s` this lane's sum.
 template <int NCH>
-__global__ void __launch_bounds__(ROWS_PER_CTA * 32)
-ln_kernel(const __half * __restrict__ x, const float * __restrict__ gamma, const float * __restrict__ beta,
-          int T, int H, __half * __restrict__ out, __half * __restrict__ out_fq, int fq_type) {
-    const int row = blockIdx.x * ROWS_PER_CTA + (threadIdx.x >> 5);
-    if (row >= T) return;
-    const int lane = threadIdx.x & 31;
+__device__ __forceinline__ void ln_row_finish(float (&v)[NCH][8], float s, int lane, int H,
+                                              const float * __restrict__ gamma, const float * __restrict__ beta,
+                                              __half * __restrict__ out_row, __half * __restrict__ out_fq_row, int fq_type) {
     const int nchunk = H / 8;
-    float v[NCH][8];
-    const uint4 * xr = reinterpret_cast<const uint4 *>(x + (size_t) row * H);
-    float s = 0.f;
-#pragma unroll
-    for (int i = 0; i < NCH; ++i) {
-        const int c = lane + 32 * i;
-        if (c < nchunk) {
-            const uint4 u = __ldg(xr + c);
-            const __half2 * h = reinterpret_cast<const __half2 *>(&u);
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                const float2 f = __half22float2(h[e]);
-                v[i][2 * e] = f.x; v[i][2 * e + 1] = f.y;
-                s += f.x + f.y;
-            }
-        } else {
-#pragma unroll
-            for (int e = 0; e < 8; ++e) v[i][e] = 0.f;
-        }
-    }
     const float mean = warp_sum(s) / (float) H;
     float s2 = 0.f;
 #pragma unroll
@@ -184,8 +39,8 @@ ln_kernel(const __half * __restrict__ x, const float * __restrict__ gamma, const
     }
     const float var = warp_sum(s2) / (float) H;
     const float scale = 1.0f / sqrtf(var + 1e-5f);
-    uint4 * orow = reinterpret_cast<uint4 *>(out + (size_t) row * H);
-    uint4 * qrow = out_fq ? reinterpret_cast<uint4 *>(out_fq + (size_t) row * H) : nullptr;
+    uint4 * orow = reinterpret_cast<uint4 *>(out_row);
+    uint4 * qrow = reinterpret_cast<uint4 *>(out_fq_row);
 #pragma unroll
     for (int i = 0; i < NCH; ++i) {
         const int c = lane + 32 * i;
@@ -227,17 +82,128 @@ ln_kernel(const __half * __restrict__ x, const float * __restrict__ gamma, const
     }
 }
 
-// one CTA per sentence; thread = (8-column chunk, token stripe)
-__global__ void __launch_bounds__(256)
+// K3.
+template <int NCH>
+__global__ void __launch_bounds__(ROWS_PER_CTA * 32)
+ln_kernel(const __half * __restrict__ x, const float * __restrict__ gamma, const float * __restrict__ beta,
+          int T, int H, __half * __restrict__ out, __half * __restrict__ out_fq, int fq_type) {
+    const int row = blockIdx.x * ROWS_PER_CTA + (threadIdx.x >> 5);
+    if (row >= T) return;
+    const int lane = threadIdx.x & 31;
+    const int nchunk = H / 8;
+    float v[NCH][8];
+    const uint4 * xr = reinterpret_cast<const uint4 *>(x + (size_t) row * H);
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+        const int c = lane + 32 * i;
+        if (c < nchunk) {
+            const uint4 u = __ldg(xr + c);
+            const __half2 * h = reinterpret_cast<const __half2 *>(&u);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float2 f = __half22float2(h[e]);
+                v[i][2 * e] = f.x; v[i][2 * e + 1] = f.y;
+                s += f.x + f.y;
+            }
+        } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[i][e] = 0.f;
+        }
+    }
+    ln_row_finish<NCH>(v, s, lane, H, gamma, beta, out + (size_t) row * H, out_fq ? out_fq + (size_t) row * H : nullptr, fq_type);
+}
+
+// K0.  Fused word-row gather (decoded from the table's own type) + (position + token-type-0) row + LayerNorm.
+// Same chunk ownership as K3: lane l takes the 8-value chunks l + 32 i, i.e. for a q4 table 8 of a block's
+// 16 payload bytes (file nibble order: byte j = e[j] | e[j+16] << 4) and the block's scale.  The position of
+// a packed token inside its sentence comes from a warp-cooperative 32-way search over cu_seqlens.
+template <int NCH>
+__global__ void __launch_bounds__(ROWS_PER_CTA * 32)
+embed_ln_kernel(const DevTable word, const float * __restrict__ postype,
+                const float * __restrict__ gamma, const float * __restrict__ beta,
+                const int32_t * __restrict__ ids, const int32_t * __restrict__ cu, int n_sent, int T, int H,
+                __half * __restrict__ out, __half * __restrict__ out_fq, int fq_type) {
+    const int row = blockIdx.x * ROWS_PER_CTA + (threadIdx.x >> 5);
+    if (row >= T) return;
+    const int lane = threadIdx.x & 31;
+    const int nchunk = H / 8, nb = H / 32;
+    int id = __ldg(ids + row);
+    if (id < 0 || id >= word.rows) id = 0;                  // never read out of the table
+    float v[NCH][8];
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+        const int c = lane + 32 * i;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[i][e] = 0.f;
+        if (c >= nchunk) continue;
+        if (word.type == W_F32) {
+            const float4 * q = reinterpret_cast<const float4 *>(reinterpret_cast<const float *>(word.data) + (size_t) id * H) + 2 * c;
+            const float4 f0 = __ldg(q), f1 = __ldg(q + 1);
+            v[i][0] = f0.x; v[i][1] = f0.y; v[i][2] = f0.z; v[i][3] = f0.w;
+            v[i][4] = f1.x; v[i][5] = f1.y; v[i][6] = f1.z; v[i][7] = f1.w;
+        } else if (word.type == W_F16) {
+            const uint4 u = __ldg(reinterpret_cast<const uint4 *>(reinterpret_cast<const __half *>(word.data) + (size_t) id * H) + c);
+            const __half2 * h = reinterpret_cast<const __half2 *>(&u);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) { const float2 f = __half22float2(h[e]); v[i][2 * e] = f.x; v[i][2 * e + 1] = f.y; }
+        } else {
+            const size_t blk = (size_t) id * nb + (c >> 2);
+            const int k = c & 3;                             // values 8k .. 8k+7 of the block
+            const uint2 u = __ldg(reinterpret_cast<const uint2 *>(word.data) + blk * 2 + (k & 1));
+            const int sh = (k >> 1) * 4;
+            const float d = __half2float(__ldg(word.qd + blk));
+            const float m = word.type == W_Q4_1 ? __half2float(__ldg(word.qm + blk)) : 0.f;
+            const uint32_t w[2] = {u.x, u.y};
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int qv = (int) ((w[j >> 2] >> (8 * (j & 3) + sh)) & 15u);
+                v[i][j] = word.type == W_Q4_0 ? (float) (qv - 8) * d : (float) qv * d + m;
+            }
+        }
+    }
+    // sentence of this packed token: largest s with cu[s] <= row, 32 pivots per round
+    int lo = 0, hi = n_sent;
+    while (hi - lo > 1) {
+        const int step = (hi - lo + 31) / 32;
+        const int idx = lo + lane * step;
+        const bool le = idx < hi && __ldg(cu + idx) <= row;
+        const unsigned mask = __ballot_sync(0xffffffffu, le);  // a prefix of lanes (cu is sorted, lane 0 always set)
+        const int kk = 31 - __clz((int) mask);
+        lo += kk * step;
+        hi = min(hi, lo + step);
+    }
+    const int pos = row - __ldg(cu + lo);
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+        const int c = lane + 32 * i;
+        if (c < nchunk) {
+            const float4 * q = reinterpret_cast<const float4 *>(postype + (size_t) pos * H) + 2 * c;
+            const float4 f0 = __ldg(q), f1 = __ldg(q + 1);
+            v[i][0] += f0.x; v[i][1] += f0.y; v[i][2] += f0.z; v[i][3] += f0.w;
+            v[i][4] += f1.x; v[i][5] += f1.y; v[i][6] += f1.z; v[i][7] += f1.w;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) s += v[i][e];
+        }
+    }
+    ln_row_finish<NCH>(v, s, lane, H, gamma, beta, out + (size_t) row * H, out_fq ? out_fq + (size_t) row * H : nullptr, fq_type);
+}
+
+// one CTA per sentence; thread = (8-column chunk, token stripe).  1024 threads keep enough 16-B loads in
+// flight per SM for a grid of only n_sent CTAs; the stripe sums are combined in a fixed order (deterministic).
+constexpr int POOL_THREADS = 1024;
+__global__ void __launch_bounds__(POOL_THREADS)
 pool_norm_kernel(const __half * __restrict__ x, const int32_t * __restrict__ cu, int H, float * __restrict__ out) {
     extern __shared__ float sm[];                       // [stripes][H] then reduction scratch
     const int sent = blockIdx.x;
     const int t0 = cu[sent], len = cu[sent + 1] - t0;
     const int ncol = H / 8;
-    const int stripes = 256 / ncol;
+    const int stripes = POOL_THREADS / ncol;
     const int c = threadIdx.x % ncol, sidx = threadIdx.x / ncol;
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (sidx < stripes) {
+#pragma unroll 4
         for (int t = sidx; t < len; t += stripes) {
             const uint4 u = __ldg(reinterpret_cast<const uint4 *>(x + (size_t) (t0 + t) * H) + c);
             const __half2 * h = reinterpret_cast<const __half2 *>(&u);
@@ -254,22 +220,26 @@ pool_norm_kernel(const __half * __restrict__ x, const int32_t * __restrict__ cu,
     // masked mean (weights 1/len on valid tokens, bert.cpp:912) and sum of squares
     const float inv_len = 1.0f / (float) len;
     float ss = 0.f;
-    for (int i = threadIdx.x; i < H; i += 256) {
+    float pooled[2] = {0.f, 0.f};                       // H <= 1024 -> at most one column per thread ... (two kept for safety)
+    int np = 0;
+    for (int i = threadIdx.x; i < H; i += POOL_THREADS) {
         float s = 0.f;
         for (int k = 0; k < stripes; ++k) s += sm[k * H + i];
         s *= inv_len;
-        sm[i] = s;                                      // stripe 0 slot now holds the pooled value
+        if (np < 2) pooled[np] = s;
+        ++np;
         ss += s * s;
     }
-    __shared__ float red[8];
+    __shared__ float red[POOL_THREADS / 32];
     ss = warp_sum(ss);
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
     __syncthreads();
     float tot = 0.f;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) tot += red[k];
+    for (int k = 0; k < POOL_THREADS / 32; ++k) tot += red[k];
     const float inv_norm = 1.0f / sqrtf(tot);           // no epsilon (bert.cpp:1092-1094)
-    for (int i = threadIdx.x; i < H; i += 256) out[(size_t) sent * H + i] = sm[i] * inv_norm;
+    np = 0;
+    for (int i = threadIdx.x; i < H; i += POOL_THREADS) { out[(size_t) sent * H + i] = pooled[np < 2 ? np : 1] * inv_norm; ++np; }
 }
 
 }  // namespace
@@ -278,8 +248,12 @@ cudaError_t launch_embed_ln(const DevTable & word, const float * postype, const 
                             const int32_t * ids, const int32_t * cu_seqlens, int n_sent, int T, int H,
                             __half * out, __half * out_fq, int fq_type, cudaStream_t st) {
     if (T <= 0) return cudaSuccess;
-    embed_ln_kernel<<<(T + ROWS_PER_CTA - 1) / ROWS_PER_CTA, ROWS_PER_CTA * 32, 0, st>>>(
-        word, postype, gamma, beta, ids, cu_seqlens, n_sent, T, H, out, out_fq, fq_type);
+    const int grid = (T + ROWS_PER_CTA - 1) / ROWS_PER_CTA;
+    const int nch = (H / 8 + 31) / 32;
+#define EMBED_LAUNCH(NCH_) embed_ln_kernel<NCH_><<<grid, ROWS_PER_CTA * 32, 0, st>>>( \
+        word, postype, gamma, beta, ids, cu_seqlens, n_sent, T, H, out, out_fq, fq_type)
+    if (nch <= 1) EMBED_LAUNCH(1); else if (nch == 2) EMBED_LAUNCH(2); else if (nch == 3) EMBED_LAUNCH(3); else EMBED_LAUNCH(4);
+#undef EMBED_LAUNCH
     return cudaGetLastError();
 }
 
@@ -298,9 +272,10 @@ cudaError_t launch_ln(const __half * x, const float * gamma, const float * beta,
 cudaError_t launch_pool_norm(const __half * x, const int32_t * cu_seqlens, int n_sent, int H,
                              float * out, cudaStream_t st) {
     if (n_sent <= 0) return cudaSuccess;
-    const int stripes = 256 / (H / 8);
+    if (H > 2 * POOL_THREADS) return cudaErrorInvalidValue;
+    const int stripes = POOL_THREADS / (H / 8);
     const size_t smem = (size_t) (stripes > 0 ? stripes : 1) * H * sizeof(float);
-    pool_norm_kernel<<<n_sent, 256, smem, st>>>(x, cu_seqlens, H, out);
+    pool_norm_kernel<<<n_sent, POOL_THREADS, smem, st>>>(x, cu_seqlens, H, out);
     return cudaGetLastError();
 }
 
