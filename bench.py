@@ -32,6 +32,7 @@ WORKLOADS = {
     "tiny-q4_0-b64-s64": ("tiny-d64", "q4_0", 64, 64),
 }
 DEFAULT_WORKLOAD = "bge-base-q4_0-b512-s512"
+NCU_GEMM_DRAM_BYTES_PER_LAUNCH = 960e6    # measured, see profiles/r1_final.md
 
 
 def shard_range(n_items, rank, world):
@@ -240,6 +241,24 @@ def main():
                 "share_of_step": gemm_ms / total_prof_ms if total_prof_ms else None,
                 "by_kernel_ms": {k: round(v[0], 3) for k, v in prof.items()},
                 "whole_forward_tflops": (gemm_flops + attn_flops) * world / (ms / args.steps / 1e3) / 1e12 / world}
+
+    # dram bytes per launch of the dominant kernel from `ncu --set full` (profiles/r1_final.md), default workload only
+    if args.workload == DEFAULT_WORKLOAD:
+        roofline["traffic"] = NCU_GEMM_DRAM_BYTES_PER_LAUNCH
+        roofline["traffic_note"] = "dram__bytes_read.sum + dram__bytes_write.sum, mean over the 4 GEMMs of a layer at 131072 tokens (profiles/r1_final.md)"
+    # the HBM-bound row kernels against the measured copy bandwidth (algorithmic bytes)
+    wbytes = {"f32": 4.0, "f16": 2.0, "q4_0": 18.0 / 32, "q4_1": 20.0 / 32}[ftype]
+    twin = 2 if "q4" in ftype else 1
+    hbm = {}
+    if prof["embed_ln"][0] > 0:
+        b = T * (H * wbytes + 2 * H * twin)
+        hbm["embed_ln"] = {"GB/s": b / (prof["embed_ln"][0] / 1e3) / 1e9, "bytes_per_step": int(b)}
+    if prof["pool_norm"][0] > 0:
+        b = T * H * 2 + n_sent * H * 4
+        hbm["pool_norm"] = {"GB/s": b / (prof["pool_norm"][0] / 1e3) / 1e9, "bytes_per_step": int(b)}
+    for v in hbm.values():
+        v["frac_of_hbm_peak"] = v["GB/s"] / peaks["hbm_gbs"]
+    roofline["hbm_bound_kernels"] = hbm
 
     line = {"metric": "embeddings/s", "value": value, "unit": "embeddings/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
