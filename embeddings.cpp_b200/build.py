@@ -53,6 +53,10 @@ def build(force=False, verbose=True):
         for out in ex.map(run, jobs):
             if verbose and out.strip():
                 print(out, file=sys.stderr)
+    # timer shim the reference's example programs link as `ggml` (include/ggml.h)
+    shim_src, shim = os.path.join(HERE, "shim", "ggml_time.c"), os.path.join(LIB, "libggml.so")
+    if force or _newer(shim_src, shim):
+        run([os.environ.get("CC", "gcc"), "-O2", "-fPIC", "-shared", "-I", os.path.join(HERE, "..", "include"), "-o", shim, shim_src])
     lib = os.path.join(LIB, "libbert.so")
     if jobs or not os.path.exists(lib):
         run([NVCC, "-shared", "-cudart", "static", "-o", lib] + objs + ["-lpthread", "-ldl", "-lrt"])

@@ -91,6 +91,27 @@ struct ItemWalk {
 __device__ __forceinline__ float ex2f(float x) {
     float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y;
 }
+// 2^x for a pair on the FMA / ALU pipes instead of the MUFU (which is this kernel's bottleneck at 16
+// results/clk/SM): round-to-nearest split x = n + r with the 1.5 * 2^23 constant, degree-3 minimax
+// polynomial for 2^r on [-0.5, 0.5] (max relative error 7.5e-5, well under the fp16 rounding of P), n added
+// straight into the exponent field.  x <= ~8 here; everything below -125 (incl. the -inf of masked keys)
+// is clamped and comes out as ~2^-125, which rounds to 0 in fp16.
+__device__ __forceinline__ float2 ex2_poly2(float2 x) {
+    const float magic = 12582912.f;
+    x.x = fmaxf(x.x, -125.f); x.y = fmaxf(x.y, -125.f);
+    const float2 t = __fadd2_rn(x, make_float2(magic, magic));
+    const float2 n = __fadd2_rn(t, make_float2(-magic, -magic));
+    const float2 r = __fadd2_rn(x, make_float2(-n.x, -n.y));
+    float2 q = __ffma2_rn(r, make_float2(0.055171531f, 0.055171531f), make_float2(0.24261111f, 0.24261111f));
+    q = __ffma2_rn(q, r, make_float2(0.69326103f, 0.69326103f));
+    q = __ffma2_rn(q, r, make_float2(0.99992806f, 0.99992806f));
+    return make_float2(__uint_as_float(__float_as_uint(q.x) + (__float_as_uint(t.x) << 23)),
+                       __uint_as_float(__float_as_uint(q.y) + (__float_as_uint(t.y) << 23)));
+}
+#ifndef BERT_ATTN_POLY_EVERY
+#define BERT_ATTN_POLY_EVERY 4
+#endif
+constexpr int kPolyEvery = BERT_ATTN_POLY_EVERY;   // every kPolyEvery-th pair of a block takes the polynomial path (0: all on the MUFU)
 __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
     __half2 h = __floats2half2_rn(a, b);
     return *reinterpret_cast<uint32_t *>(&h);
@@ -217,7 +238,6 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     } else {
         // ------------------------------------------------------------ softmax + output (4 warps)
         const int q = warp & 3;                               // TMEM lane quadrant of this warp
-        const int row = q * 32 + lane;                        // query row inside the tile
         const uint32_t lane_base = tmem_base + ((uint32_t) (q * 32) << 16);
         uint32_t g = 0;
         ItemWalk walk(p, blockIdx.x, gridDim.x, total_items);
@@ -277,7 +297,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
                     const float2 x = __ffma2_rn(make_float2(s[2 * j], s[2 * j + 1]), sc2, nm2);
-                    const float2 e = make_float2(ex2f(x.x), ex2f(x.y));
+                    const float2 e = (kPolyEvery > 0 && j % (kPolyEvery > 0 ? kPolyEvery : 1) == kPolyEvery - 1)
+                                         ? ex2_poly2(x) : make_float2(ex2f(x.x), ex2f(x.y));
                     sum[j & 1] = __fadd2_rn(sum[j & 1], e);
                     pk[j] = pack_h2(e.x, e.y);
                 }
