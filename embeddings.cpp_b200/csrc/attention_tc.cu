@@ -11,15 +11,10 @@
 //   warp 1     MMA issuer (one elected lane): S_b = Q K_b^T into a double-buffered TMEM tile
 //              (M=128, N=64), then O += P_b V_b with P read from TMEM (A operand) and V as an
 //              MN-major smem operand -- V is never transposed
-//   warps 4-7  softmax: one query row per thread (tcgen05.ld 32x32b), running max / sum in f32
-//              registers, exp2 on the MUFU (every 4th pair on the FMA pipe), P written back over S as
-//              packed fp16 (tcgen05.st).  The running max is only moved (and O rescaled in TMEM) when a
-//              block exceeds it by more than 2^8, so the accumulator normally stays untouched in TMEM.
-//   warps 8-11 output: wait for the item's last P V, pull O out of TMEM (which frees it for the next
-//              item), scale by 1 / l (row sums handed over through smem), q8 fake-quant, coalesced rows.
-//              The softmax warps are the kernel's critical resource; taking the per-item tail (22 % of
-//              their time, more for short sentences) off them lets them start the next item at once.
-// Roles are warpgroup-aligned (warps 2-3 idle) so that registers are re-balanced with setmaxnreg.
+//   warps 2-5  softmax: one query row per thread (tcgen05.ld 32x32b), running max / sum in f32
+//              registers, exp2 on the MUFU, P written back over S as packed fp16 (tcgen05.st).
+//              The running max is only moved (and O rescaled in TMEM) when a block exceeds it by
+//              more than 2^8, so the accumulator normally stays untouched in TMEM until the end.
 // Issue order S_0, S_1, PV_0, S_2, PV_1, ... keeps the tensor pipe one score block ahead of the
 // softmax warps; the second CTA on the SM fills the remaining bubbles.
 #include "kernels.cuh"
@@ -33,15 +28,12 @@ constexpr int AQ = 128;            // queries per item
 constexpr int AK = 64;             // keys per block
 constexpr int AD = 64;             // head size
 constexpr int KV_STAGES = 4;
-constexpr int ATT_TC_THREADS = 384;
-constexpr int kRegsCtrl = 24, kRegsSoftmax = 144, kRegsOut = 72;     // x 128 threads = 384 x 80 (launch)
-static_assert(kRegsCtrl + kRegsSoftmax + kRegsOut == 3 * 80, "setmaxnreg pool");
+constexpr int ATT_TC_THREADS = 192;
 constexpr int kQBytes = AQ * AD * 2;          // 16 KB
 constexpr int kKVBytes = AK * AD * 2;         // 8 KB each for K and V
 constexpr int Q_STAGES = 1;
 constexpr int kOutStage = 4 * 4096;            // per softmax warp: [32 rows][128 B] staging for coalesced output rows
-constexpr int kLBytes = 2 * AQ * 4;              // row sums of the last two items (softmax -> output warps)
-constexpr int kAttSmem = Q_STAGES * kQBytes + KV_STAGES * 2 * kKVBytes + kOutStage + kLBytes + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int kAttSmem = Q_STAGES * kQBytes + KV_STAGES * 2 * kKVBytes + kOutStage + 1024 /*align*/ + 256 /*barriers*/;
 constexpr uint32_t TM_S = 0;       // S buffers at columns 0 and 64 (P aliases the first 32 columns of each)
 constexpr uint32_t TM_O = 128;     // O accumulator: 64 columns
 constexpr uint32_t TM_COLS = 256;
@@ -136,8 +128,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     uint8_t * smem_k = smem + Q_STAGES * kQBytes;                    // KV_STAGES x 8 KB
     uint8_t * smem_v = smem_k + KV_STAGES * kKVBytes;                // KV_STAGES x 8 KB
     uint8_t * smem_o = smem_v + KV_STAGES * kKVBytes;                // 4 x 4 KB output staging
-    float * smem_l = (float *) (smem_o + kOutStage);                 // [2][128]
-    uint64_t * bars = (uint64_t *) (smem_o + kOutStage + kLBytes);
+    uint64_t * bars = (uint64_t *) (smem_o + kOutStage);
     uint64_t * q_full = bars;                   // [Q_STAGES]
     uint64_t * q_empty = bars + Q_STAGES;       // [Q_STAGES]
     uint64_t * kv_full = q_empty + Q_STAGES;    // [KV_STAGES]
@@ -146,8 +137,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     uint64_t * p_ready = s_full + 2;            // [2]
     uint64_t * pv_done = p_ready + 2;           // [2]  P V of block g has reached the accumulator (barrier g & 1)
     uint64_t * o_free = pv_done + 2;            // [1]
-    uint64_t * l_ready = o_free + 1;            // [2]  row sums of item n are in smem_l[n & 1]
-    uint32_t * tmem_slot = (uint32_t *) (l_ready + 2);
+    uint32_t * tmem_slot = (uint32_t *) (o_free + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int total_items = p.n_sent * p.n_head * p.max_qt;
@@ -160,7 +150,6 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         for (int a = 0; a < 2; ++a) { mbar_init(&s_full[a], 1); mbar_init(&p_ready[a], 4); }
         mbar_init(&pv_done[0], 1); mbar_init(&pv_done[1], 1);
         mbar_init(o_free, 4);
-        mbar_init(&l_ready[0], 4); mbar_init(&l_ready[1], 4);
         fence_mbar_init();
     }
     if (warp == 1) { tmem_alloc(tmem_slot, TM_COLS); tmem_relinquish(); }
@@ -169,9 +158,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp < 4) {
-      reg_dealloc<kRegsCtrl>();
-      if (warp == 0) {
+    if (warp == 0) {
         // ------------------------------------------------------------ TMA producer
         if (lane == 0) {
             uint32_t kv_it = 0, item_n = 0;
@@ -195,7 +182,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                 ++item_n;
             }
         }
-      } else if (warp == 1) {
+    } else if (warp == 1) {
         // ------------------------------------------------------------ MMA issuer
         constexpr uint32_t idesc_s = umma_idesc_f16(AQ, AK);            // Q (K-major) x K (K-major)
         constexpr uint32_t idesc_o = umma_idesc_f16(AQ, AD, 1);         // P (TMEM) x V (MN-major)
@@ -248,13 +235,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
             g += nb;
             ++item_n;
         }
-      }
-    } else if (warp < 8) {
-        // ------------------------------------------------------------ softmax (4 warps)
-        reg_alloc<kRegsSoftmax>();
+    } else {
+        // ------------------------------------------------------------ softmax + output (4 warps)
         const int q = warp & 3;                               // TMEM lane quadrant of this warp
-        const int row = q * 32 + lane;                        // query row inside the tile
-        uint32_t item_n = 0;
         const uint32_t lane_base = tmem_base + ((uint32_t) (q * 32) << 16);
         uint32_t g = 0;
         ItemWalk walk(p, blockIdx.x, gridDim.x, total_items);
@@ -327,48 +310,28 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                 if (lane == 0) mbar_arrive(&p_ready[gb & 1]);
             }
             g += nb;
-            // row sums to the output warps (slot item_n & 1: the output warps have read slot n before P V_0 of item
-            // n + 1 may be issued -- o_free -- and every S block of item n + 2 is issued after that)
-            smem_l[(item_n & 1) * AQ + row] = l;
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&l_ready[item_n & 1]);
-            ++item_n;
-        }
-    } else {
-        // ------------------------------------------------------------ output (4 warps)
-        reg_dealloc<kRegsOut>();
-        const int q = warp & 3;
-        const int row = q * 32 + lane;
-        const uint32_t lane_base = tmem_base + ((uint32_t) (q * 32) << 16);
-        const bool fq = p.fq_type == W_Q4_0 || p.fq_type == W_Q4_1;
-        uint8_t * stg = smem_o + q * 4096;                      // this warp's [32 rows][128 B], 16-B chunks XOR-swizzled by row
-        uint32_t g = 0, item_n = 0;
-        ItemWalk walk(p, blockIdx.x, gridDim.x, total_items);
-        while (walk.advance(p)) {
-            const Item it = walk.cur;
-            if (!it.valid()) continue;
-            const int len = it.len();
-            g += (len + AK - 1) / AK;
-            mbar_wait(&l_ready[item_n & 1], (item_n >> 1) & 1);
-            const float inv = 1.f / smem_l[(item_n & 1) * AQ + row];
-            const float2 inv2 = make_float2(inv, inv);
-            // the item's last P V (no later phase of this barrier can complete before o_free is given below)
+            // ---- finalize: O / l, optional q8 fake-quant per 32-wide block, fp16 store of valid rows
             mbar_wait(&pv_done[(g - 1) & 1], ((g - 1) >> 1) & 1);
             tc_fence_after_sync();
+            uint32_t o0[32], o1[32];
+            tmem_ld_32x32b_x32(lane_base + TM_O, o0);
+            tmem_ld_32x32b_x32(lane_base + TM_O + 32, o1);
+            tmem_ld_wait();
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(o_free);
+            const float inv = 1.f / l;
+            const float2 inv2 = make_float2(inv, inv);
+            const bool fq = p.fq_type == W_Q4_0 || p.fq_type == W_Q4_1;
+            uint8_t * stg = smem_o + q * 4096;                  // this warp's [32 rows][128 B], 16-B chunks XOR-swizzled by row
 #pragma unroll
             for (int hh = 0; hh < 2; ++hh) {
-                uint32_t o[32];
-                tmem_ld_32x32b_x32(lane_base + TM_O + hh * 32, o);
-                tmem_ld_wait();
-                if (hh == 1) {                                  // O is in registers: the next item may accumulate
-                    tc_fence_before_sync();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(o_free);
-                }
                 float2 v[16];
 #pragma unroll
-                for (int j = 0; j < 16; ++j)
+                for (int j = 0; j < 16; ++j) {
+                    const uint32_t * o = hh == 0 ? o0 : o1;
                     v[j] = __fmul2_rn(make_float2(__uint_as_float(o[2 * j]), __uint_as_float(o[2 * j + 1])), inv2);
+                }
                 if (fq) fake_quant32_v2(v, p.fq_type);
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
@@ -392,7 +355,6 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                 }
             }
             __syncwarp();                                       // staging is reused by the next item
-            ++item_n;
         }
     }
 
