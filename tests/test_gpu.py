@@ -212,3 +212,38 @@ def test_full_size_properties_bge_base(pkg):
     e2 = m.encode([texts[i] for i in perm])
     assert np.abs(e2 - e[perm]).max() <= 4e-3
     m.close()
+
+
+def test_in_process_sharding_over_all_visible_gpus(pkg):
+    """One process, every visible GPU (what a drop-in caller of bert_encode_batch gets on a multi-GPU box):
+    micro-batches are dealt to the replicas with no collective; results equal the single-GPU ones bit for bit."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs (run under gpurun --gpus 2)")
+    model = synth.model_path("tiny-d64", "q4_0")
+    mf = fileformat.read_model(model)
+    texts = synth.texts_var_len(mf.vocab, 700, 2, 200, seed=21, cjk=True)
+    old = {k: os.environ.get(k) for k in ("BERT_CUDA_DEVICES", "BERT_MICROBATCH_TOKENS")}
+    os.environ["BERT_MICROBATCH_TOKENS"] = "2048"
+    try:
+        os.environ["BERT_CUDA_DEVICES"] = "0"
+        m1 = pkg.BertModel(model)
+        assert m1.n_devices() == 1
+        one = m1.encode(texts)
+        m1.close()
+        del os.environ["BERT_CUDA_DEVICES"]
+        mN = pkg.BertModel(model)
+        assert mN.n_devices() == torch.cuda.device_count()
+        many = mN.encode(texts)
+        again = mN.encode(texts[:5])
+        mN.close()
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+    assert np.isfinite(many).all() and np.allclose(np.linalg.norm(many, axis=1), 1.0, atol=2e-4)
+    # chunking differs (the chunk target scales with the GPU count), so micro-batch composition differs: rounding only
+    assert np.abs(many - one).max() <= 4e-3
+    assert np.abs(again - one[:5]).max() <= 4e-3
