@@ -78,12 +78,24 @@ def lib():
     L.bertx_bench_attention.argtypes = [c_i32, c_i32, c_i32, c_i32, c_i32, pf]
     L.bertx_selftest_attention.restype = c_i32
     L.bertx_selftest_attention.argtypes = [c_i32, c_i32, c_i32, c_i32, c_i32, pf, pf]
+    L.bertx_quantize_file.restype = c_i32
+    L.bertx_quantize_file.argtypes = [cp, cp, c_i32]
     _lib = L
     return L
 
 
 def _fp(a):
     return a.ctypes.data_as(ctypes.POINTER(ctypes.c_float))
+
+
+def _row_ptrs(out):
+    """float** over the rows of a 2-D float32 array: the addresses are computed in numpy (one vector op) instead
+    of one ctypes cast per row (examples/sample_dylib.py:50-51 does the latter; 1738 rows cost milliseconds)."""
+    addr = out.ctypes.data + np.arange(out.shape[0], dtype=np.uint64) * np.uint64(out.strides[0])
+    out_ptrs = np.ascontiguousarray(addr, dtype=np.uint64)
+    p = ctypes.cast(out_ptrs.ctypes.data, ctypes.POINTER(ctypes.POINTER(ctypes.c_float)))
+    p._keep = out_ptrs                      # the pointer table must outlive the call
+    return p
 
 
 def _ip(a):
@@ -122,8 +134,7 @@ class BertModel:
         if n == 0:
             return out
         texts = (ctypes.c_char_p * n)(*[s if isinstance(s, bytes) else s.encode("utf-8") for s in sentences])
-        rows = (ctypes.POINTER(ctypes.c_float) * n)(*[_fp(out[i]) for i in range(n)])
-        self.lib.bert_encode_batch(self.ctx, self.n_threads, batch_size, n, texts, rows)
+        self.lib.bert_encode_batch(self.ctx, self.n_threads, batch_size, n, texts, _row_ptrs(out))
         return out
 
     def tokenize(self, text, n_max=None):
@@ -144,9 +155,8 @@ class BertModel:
         arrs = [np.ascontiguousarray(t, dtype=np.int32) for t in batch_tokens]
         ptrs = (ctypes.POINTER(ctypes.c_int32) * n)(*[_ip(a) for a in arrs])
         lens = np.array([len(a) for a in arrs], dtype=np.int32)
-        rows = (ctypes.POINTER(ctypes.c_float) * n)(*[_fp(out[i]) for i in range(n)])
         fn = self.lib.bert_forward_fake_batch if fake_batch else self.lib.bert_forward_batch
-        fn(self.ctx, self.n_threads, n, ptrs, _ip(lens), rows)
+        fn(self.ctx, self.n_threads, n, ptrs, _ip(lens), _row_ptrs(out))
         return out
 
     # -- measurement extensions (bert_b200.h) -----------------------------------------
@@ -196,6 +206,13 @@ class BertModel:
             raise RuntimeError(f"bertx_profile_staged failed ({rc})")
         names = ["embed_ln", "gemm", "attention", "add_ln", "pool_norm", "other"]
         return {n: (float(ms[i]), int(cnt[i])) for i, n in enumerate(names)}
+
+
+def quantize_file(fname_inp, fname_out, itype):
+    """models/quantize.cpp's `quantize in out type` (2 = q4_0, 3 = q4_1) on the GPU; raises on failure."""
+    rc = lib().bertx_quantize_file(os.fsencode(fname_inp), os.fsencode(fname_out), itype)
+    if rc != 0:
+        raise RuntimeError(f"bertx_quantize_file failed ({rc}, see stderr)")
 
 
 def selftest_gemm(M, N, K, wtype, epilogue, seed=0):

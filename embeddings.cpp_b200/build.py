@@ -21,7 +21,7 @@ FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std
 if os.environ.get("BERT_DEBUG_WAIT"):
     FLAGS.append("-DBERT_DEBUG_WAIT")
 SOURCES = ["gemm_tc.cu", "attention.cu", "attention_tc.cu", "rowwise.cu", "upload.cu", "engine_load.cu", "engine_run.cu",
-           "api.cu", "api_ext.cu", "tokenizer.cpp", "model_file.cpp"]
+           "api.cu", "api_ext.cu", "quantize.cu", "tokenizer.cpp", "model_file.cpp"]
 
 
 def _newer(a, b):

@@ -72,6 +72,12 @@ BERT_API int32_t bertx_selftest_attention(int32_t n_sent, int32_t max_len, int32
 BERT_API int32_t bertx_bench_attention(int32_t n_sent, int32_t len, int32_t n_head, int32_t d_head, int32_t reps,
                                        float * ms_total);
 
+/* Model quantiser: fname_inp (f32 / f16 file) -> fname_out with every 2-D "*weight" tensor as
+ * q4_0 (itype 2) or q4_1 (itype 3) blocks, byte-identical to the reference's `quantize` tool
+ * (models/quantize.cpp:27-268, `./quantize in.bin out.bin type`; block arithmetic ggml.c:942-1018).  The block
+ * quantisation runs as a CUDA kernel; returns 0 on success, non-zero (+ message on stderr) otherwise. */
+BERT_API int32_t bertx_quantize_file(const char * fname_inp, const char * fname_out, int32_t itype);
+
 #ifdef __cplusplus
 }
 #endif

@@ -247,3 +247,29 @@ def test_in_process_sharding_over_all_visible_gpus(pkg):
     # chunking differs (the chunk target scales with the GPU count), so micro-batch composition differs: rounding only
     assert np.abs(many - one).max() <= 4e-3
     assert np.abs(again - one[:5]).max() <= 4e-3
+
+
+@pytest.mark.parametrize("shape", ["tiny-d64", "all-MiniLM-L6-v2"])
+def test_gpu_quantizer_writes_the_reference_quantizers_bytes(pkg, shape, tmp_path):
+    """bertx_quantize_file (CUDA kernel) == models/quantize.cpp output, byte for byte: against the files the
+    numpy restatement writes (itself pinned bit-exact to the reference binary, tests/test_oracle.py) and, where
+    oracle/_ref/quantize travelled, against the reference binary run live (f16 and f32 sources)."""
+    import subprocess
+    f16 = synth.model_path(shape, "f16")
+    for itype, ft in ((2, "q4_0"), (3, "q4_1")):
+        out = str(tmp_path / f"{ft}.bin")
+        pkg.quantize_file(f16, out, itype)
+        assert open(out, "rb").read() == open(synth.model_path(shape, ft), "rb").read(), (shape, ft)
+    if os.path.exists(reflib.QUANTIZE_BIN) and shape == "tiny-d64":
+        f32 = synth.model_path(shape, "f32")
+        for src in (f16, f32):
+            for itype in (2, 3):
+                a, b = str(tmp_path / "a.bin"), str(tmp_path / "b.bin")
+                subprocess.run([reflib.QUANTIZE_BIN, src, a, str(itype)], check=True, capture_output=True)
+                pkg.quantize_file(src, b, itype)
+                assert open(a, "rb").read() == open(b, "rb").read(), (src, itype)
+    # the quantised file loads and encodes
+    m = pkg.BertModel(str(tmp_path / "q4_1.bin"))
+    e = m.encode([b"hello world"])
+    assert np.isfinite(e).all() and abs(np.linalg.norm(e[0]) - 1.0) < 1e-4
+    m.close()

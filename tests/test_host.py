@@ -158,3 +158,13 @@ def test_shard_range_properties():
             assert all(parts[i][1] == parts[i + 1][0] for i in range(w - 1))
             sizes = [b - a for a, b in parts]
             assert max(sizes) - min(sizes) <= 1
+
+
+@pytest.mark.skipif(__import__("conftest").has_gpu(), reason="checks the no-GPU failure path")
+def test_quantizer_fails_loudly_without_a_gpu(pkg, tmp_path, capfd):
+    from tools import synth
+    with pytest.raises(RuntimeError):
+        pkg.quantize_file(synth.model_path("tiny-d64", "f16"), str(tmp_path / "o.bin"), 2)
+    assert "no CUDA device" in capfd.readouterr().err
+    with pytest.raises(RuntimeError):
+        pkg.quantize_file("/nonexistent", str(tmp_path / "o.bin"), 7)      # bad type is rejected first
