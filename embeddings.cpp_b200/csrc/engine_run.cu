@@ -44,9 +44,14 @@ bool Engine::forward(Replica & r, const int32_t * d_ids, const int32_t * d_cu, i
     };
     auto end = [&]() { if (r.profiling) cudaEventRecord(r.spans.back().b, st); };
 
+    // latency path: with few tokens the GEMMs are bound by how fast ONE CTA pair can stream and dequantise its
+    // weight rows (256-wide N-tiles leave 3-12 pairs busy); 64-wide tiles spread the weights over 4x as many
+    // pairs.  The LayerNorm fusion needs the wide tiles, so small batches take the stand-alone LN kernel.
+    const bool small = T <= small_t && (hp.ftype == 2 || hp.ftype == 3);      // the N-tile override exists for q4 weights only
     auto gemm = [&](const CUtensorMap * tm, const CUtensorMap * tmo, const __half * a, const DevWeight & w,
                     const __half * res, const CUtensorMap * tmr, __half * out, int epi) {
         GemmArgs g{tm, tmo, tmr, a, &w, res, out, T, epi, fq_type};
+        g.bn_override = small ? 64 : 0;
         begin(KK_GEMM);
         L(KK_GEMM, gemm_simt ? launch_gemm_simt(g, st) : launch_gemm_tc(g, r.num_sms, st), "gemm");
         end();
@@ -79,7 +84,7 @@ bool Engine::forward(Replica & r, const int32_t * d_ids, const int32_t * d_cu, i
             L(KK_ATTN, ae, "attention");
         }
         end();
-        const bool fuse = fuse_ln && !gemm_simt && gemm_ln_fusable(ly.o) && gemm_ln_fusable(ly.ffo);
+        const bool fuse = fuse_ln && !small && !gemm_simt && gemm_ln_fusable(ly.o) && gemm_ln_fusable(ly.ffo);
         if (fuse && fuse_ln_att) {
             gemm_ln(&r.tm_ctx, r.ctx, ly.o, r.x, &r.tr_x, ly.ln_att_g, ly.ln_att_b, r.x1, &r.to_x1, &r.to_x1q);
         } else {

@@ -769,7 +769,8 @@ bool gemm_ln_fusable(const DevWeight & w) {
 
 cudaError_t launch_gemm_tc(const GemmArgs & g, int num_sms, cudaStream_t st) {
     const DevWeight & w = *g.w;
-    const int bn = w.bn;
+    int bn = w.bn;
+    if (g.bn_override > 0 && (w.type == W_Q4_0 || w.type == W_Q4_1) && w.N % g.bn_override == 0 && !(g.epilogue & EPI_LN)) bn = g.bn_override;
     if (bn == 0 || w.K % BK != 0) return cudaErrorInvalidValue;
     if (g.epilogue & EPI_LN) {
         if (!gemm_ln_fusable(w) || (g.epilogue & EPI_GELU) || !(g.epilogue & EPI_RESIDUAL) || !(g.epilogue & EPI_BIAS)) return cudaErrorInvalidValue;

@@ -51,6 +51,9 @@ struct GemmArgs {
     const CUtensorMap * tmap_out2 = nullptr;
     const float * ln_gamma = nullptr;
     const float * ln_beta = nullptr;
+    // q4 weights only (their HBM layout does not depend on the N-tile): use this N-tile instead of w->bn.
+    // Small batches pick 64 so that 4x as many CTA pairs stream the weights (latency path).
+    int bn_override = 0;
 };
 
 int gemm_pick_bn(int N);              // N-tile (256/192/128/64) used for a weight with N rows

@@ -27,3 +27,14 @@ for n_tok in (8, 32, 128):
         ts.append((time.perf_counter() - t0) * 1e3)
     ts = np.sort(ts)
     print(f"{shape} {ftype} {n_tok:4d} tokens: median {ts[150]:.3f} ms  p99 {ts[297]:.3f} ms  min {ts[0]:.3f} ms", flush=True)
+
+# where the time goes: device time of the staged forward (CUDA events, no host work between launches) and the
+# per-kernel-class event times of one profiled forward
+for n_sent, n_tok in ((1, 32), (16, 32), (64, 32), (128, 32), (64, 128)):
+    ids, lens = m.tokenize_batch(synth.texts_exact_len(vocab, n_sent, n_tok, seed=32))
+    m.stage(ids, lens)
+    m.run_staged(reps=20)
+    ms, _ = m.run_staged(reps=200)
+    prof = m.profile_staged()
+    print(f"staged forward, {n_sent} x {n_tok} tokens: {ms / 200:.3f} ms per forward (stream time);  per class (events around each launch): "
+          + ", ".join(f"{k} {v[0]:.3f} ms / {v[1]} launches" for k, v in prof.items() if v[1]), flush=True)
