@@ -10,6 +10,7 @@
 // K/V tiles double-buffered with cp.async.  (A tcgen05/TMEM version replaces the two
 // MMAs later; the softmax and the varlen tiling stay.)
 #include "kernels.cuh"
+#include "ptx.cuh"
 
 namespace b200 {
 
@@ -69,6 +70,8 @@ template <int D>
 __global__ void __launch_bounds__(ATT_THREADS)
 attention_kernel(const __half * __restrict__ qkv, const int32_t * __restrict__ cu, int H, float scale_log2,
                  __half * __restrict__ out, int fq_type) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int sent = blockIdx.z, head = blockIdx.y, qt = blockIdx.x;
     const int t0 = cu[sent], len = cu[sent + 1] - t0;
     const int q0 = qt * BQ;
@@ -239,13 +242,11 @@ cudaError_t launch_attention(const __half * qkv, const int32_t * cu_seqlens, int
     const float scale_log2 = 1.4426950408889634f / sqrtf((float) d_head);
     dim3 grid((max_len + BQ - 1) / BQ, n_head, n_sent);
     if (d_head == 64) {
-        attention_kernel<64><<<grid, ATT_THREADS, 0, st>>>(qkv, cu_seqlens, H, scale_log2, out, fq_type);
+        return launch_pdl(attention_kernel<64>, grid, dim3(ATT_THREADS), 0, st, qkv, cu_seqlens, H, scale_log2, out, fq_type);
     } else if (d_head == 32) {
-        attention_kernel<32><<<grid, ATT_THREADS, 0, st>>>(qkv, cu_seqlens, H, scale_log2, out, fq_type);
-    } else {
-        return cudaErrorInvalidValue;
+        return launch_pdl(attention_kernel<32>, grid, dim3(ATT_THREADS), 0, st, qkv, cu_seqlens, H, scale_log2, out, fq_type);
     }
-    return cudaGetLastError();
+    return cudaErrorInvalidValue;
 }
 
 }  // namespace b200

@@ -157,6 +157,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_launch_dependents();
+    pdl_wait();                                 // everything above overlapped the tail of the previous kernel
 
     if (warp == 0) {
         // ------------------------------------------------------------ TMA producer
@@ -383,8 +385,7 @@ cudaError_t launch_attention_tc(const CUtensorMap * tm_q, const CUtensorMap * tm
     const long long total = (long long) n_sent * n_head * p.max_qt;
     if (total > 0x7fffffffLL) return cudaErrorInvalidValue;
     const int grid = (int) (total < 2LL * num_sms ? total : 2LL * num_sms);
-    attention_tc_kernel<<<grid, ATT_TC_THREADS, kAttSmem, st>>>(*tm_q, *tm_kv, p);
-    return cudaGetLastError();
+    return launch_pdl(attention_tc_kernel, dim3(grid), dim3(ATT_TC_THREADS), kAttSmem, st, *tm_q, *tm_kv, p);
 }
 
 }  // namespace b200

@@ -229,6 +229,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     cluster_sync_all();                     // the peer's barriers exist before anything signals them
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_launch_dependents();
+    pdl_wait();                             // everything above overlapped the tail of the previous kernel
 
     if (warp < CTRL_WARPS) {
       if constexpr (Q4) reg_dealloc<kRegsCtrl>();
@@ -747,10 +749,12 @@ static cudaError_t launch_one(const GemmArgs & g, int num_sms, cudaStream_t st) 
     cfg.blockDim = dim3(gemm_threads<WT>());
     cfg.dynamicSmemBytes = Cfg::kSmemBytes;
     cfg.stream = st;
-    cudaLaunchAttribute at[1];
+    cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = (unsigned) csize; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-    cfg.attrs = at; cfg.numAttrs = 1;
+    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 2 : 1;
     return cudaLaunchKernelEx(&cfg, kern, *g.tmap_a, w.tmap, *g.tmap_out, *tres, *tout2, p);
 }
 

@@ -5,6 +5,8 @@
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
+#include <utility>
 
 namespace b200 {
 
@@ -96,6 +98,25 @@ cudaError_t launch_attention_ref(const __half * qkv, const int32_t * cu_seqlens,
 // K4: masked mean over the sentence's tokens + L2 normalise -> f32 [n_sent][H]
 cudaError_t launch_pool_norm(const __half * x, const int32_t * cu_seqlens, int n_sent, int H,
                              float * out, cudaStream_t st);
+
+// Every kernel of the forward is launched through this helper: with programmatic dependent launch (PDL) the
+// next kernel's launch latency and prologue (barrier init, TMEM allocation, descriptor prefetch) overlap the tail
+// of the current one; each kernel executes griddepcontrol.wait before its first dependent global access.
+// BERT_PDL=0 launches with plain stream order.
+inline bool pdl_enabled() {
+    static const bool on = [] { const char * e = getenv("BERT_PDL"); return !(e && atoi(e) == 0); }();
+    return on;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args &&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+}
 
 // upload-time transforms (device side)
 cudaError_t launch_f32_to_f16(const float * in, __half * out, size_t n, cudaStream_t st);

@@ -24,6 +24,14 @@ __device__ __forceinline__ bool elect_one() {
 }
 
 // Warpgroup register re-allocation (all 4 warps of an aligned warpgroup execute the same one)
+// Programmatic dependent launch: a kernel launched with the stream-serialisation attribute may start while its
+// predecessor is still running; it must execute pdl_wait() before it touches global memory the predecessor reads
+// or writes (the wait returns once the predecessor grid has completed and its writes are visible).
+// pdl_launch_dependents() lets the successor's CTAs be scheduled as soon as SM resources free up.  Both are no-ops
+// for a kernel launched without the attribute.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 template <int N> __device__ __forceinline__ void reg_alloc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" :: "n"(N)); }
 template <int N> __device__ __forceinline__ void reg_dealloc() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" :: "n"(N)); }
 

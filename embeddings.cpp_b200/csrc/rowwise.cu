@@ -7,6 +7,7 @@
 // 512-B line group; the q8 activation fake-quant (one scale per 32 values, ggml.c:1146-1300 /
 // 1425-1480) is a 4-lane shuffle.  Statistics are f32 warp-shuffle reductions.
 #include "kernels.cuh"
+#include "ptx.cuh"
 
 namespace b200 {
 
@@ -87,6 +88,8 @@ template <int NCH>
 __global__ void __launch_bounds__(ROWS_PER_CTA * 32)
 ln_kernel(const __half * __restrict__ x, const float * __restrict__ gamma, const float * __restrict__ beta,
           int T, int H, __half * __restrict__ out, __half * __restrict__ out_fq, int fq_type) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int row = blockIdx.x * ROWS_PER_CTA + (threadIdx.x >> 5);
     if (row >= T) return;
     const int lane = threadIdx.x & 31;
@@ -124,6 +127,8 @@ embed_ln_kernel(const DevTable word, const float * __restrict__ postype,
                 const float * __restrict__ gamma, const float * __restrict__ beta,
                 const int32_t * __restrict__ ids, const int32_t * __restrict__ cu, int n_sent, int T, int H,
                 __half * __restrict__ out, __half * __restrict__ out_fq, int fq_type) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int row = blockIdx.x * ROWS_PER_CTA + (threadIdx.x >> 5);
     if (row >= T) return;
     const int lane = threadIdx.x & 31;
@@ -196,6 +201,8 @@ constexpr int POOL_THREADS = 1024;
 __global__ void __launch_bounds__(POOL_THREADS)
 pool_norm_kernel(const __half * __restrict__ x, const int32_t * __restrict__ cu, int H, float * __restrict__ out) {
     extern __shared__ float sm[];                       // [stripes][H] then reduction scratch
+    pdl_launch_dependents();
+    pdl_wait();
     const int sent = blockIdx.x;
     const int t0 = cu[sent], len = cu[sent + 1] - t0;
     const int ncol = H / 8;
@@ -250,11 +257,13 @@ cudaError_t launch_embed_ln(const DevTable & word, const float * postype, const 
     if (T <= 0) return cudaSuccess;
     const int grid = (T + ROWS_PER_CTA - 1) / ROWS_PER_CTA;
     const int nch = (H / 8 + 31) / 32;
-#define EMBED_LAUNCH(NCH_) embed_ln_kernel<NCH_><<<grid, ROWS_PER_CTA * 32, 0, st>>>( \
+#define EMBED_LAUNCH(NCH_) launch_pdl(embed_ln_kernel<NCH_>, dim3(grid), dim3(ROWS_PER_CTA * 32), 0, st, \
         word, postype, gamma, beta, ids, cu_seqlens, n_sent, T, H, out, out_fq, fq_type)
-    if (nch <= 1) EMBED_LAUNCH(1); else if (nch == 2) EMBED_LAUNCH(2); else if (nch == 3) EMBED_LAUNCH(3); else EMBED_LAUNCH(4);
+    if (nch <= 1) return EMBED_LAUNCH(1);
+    if (nch == 2) return EMBED_LAUNCH(2);
+    if (nch == 3) return EMBED_LAUNCH(3);
+    return EMBED_LAUNCH(4);
 #undef EMBED_LAUNCH
-    return cudaGetLastError();
 }
 
 cudaError_t launch_ln(const __half * x, const float * gamma, const float * beta, int T, int H,
@@ -262,11 +271,12 @@ cudaError_t launch_ln(const __half * x, const float * gamma, const float * beta,
     if (T <= 0) return cudaSuccess;
     const int grid = (T + ROWS_PER_CTA - 1) / ROWS_PER_CTA;
     const int nch = (H / 8 + 31) / 32;
-    if (nch <= 1) ln_kernel<1><<<grid, ROWS_PER_CTA * 32, 0, st>>>(x, gamma, beta, T, H, out, out_fq, fq_type);
-    else if (nch == 2) ln_kernel<2><<<grid, ROWS_PER_CTA * 32, 0, st>>>(x, gamma, beta, T, H, out, out_fq, fq_type);
-    else if (nch == 3) ln_kernel<3><<<grid, ROWS_PER_CTA * 32, 0, st>>>(x, gamma, beta, T, H, out, out_fq, fq_type);
-    else ln_kernel<4><<<grid, ROWS_PER_CTA * 32, 0, st>>>(x, gamma, beta, T, H, out, out_fq, fq_type);
-    return cudaGetLastError();
+#define LN_LAUNCH(NCH_) launch_pdl(ln_kernel<NCH_>, dim3(grid), dim3(ROWS_PER_CTA * 32), 0, st, x, gamma, beta, T, H, out, out_fq, fq_type)
+    if (nch <= 1) return LN_LAUNCH(1);
+    if (nch == 2) return LN_LAUNCH(2);
+    if (nch == 3) return LN_LAUNCH(3);
+    return LN_LAUNCH(4);
+#undef LN_LAUNCH
 }
 
 cudaError_t launch_pool_norm(const __half * x, const int32_t * cu_seqlens, int n_sent, int H,
@@ -275,8 +285,7 @@ cudaError_t launch_pool_norm(const __half * x, const int32_t * cu_seqlens, int n
     if (H > 2 * POOL_THREADS) return cudaErrorInvalidValue;
     const int stripes = POOL_THREADS / (H / 8);
     const size_t smem = (size_t) (stripes > 0 ? stripes : 1) * H * sizeof(float);
-    pool_norm_kernel<<<n_sent, POOL_THREADS, smem, st>>>(x, cu_seqlens, H, out);
-    return cudaGetLastError();
+    return launch_pdl(pool_norm_kernel, dim3(n_sent), dim3(POOL_THREADS), smem, st, x, cu_seqlens, H, out);
 }
 
 }  // namespace b200
