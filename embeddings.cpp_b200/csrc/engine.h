@@ -85,6 +85,7 @@ struct Engine {
     bool fuse_ln_att = true;                   // also fuse the LayerNorm after the attention-output GEMM (BERT_FUSE_LN=1: ffn-out only)
     bool fuse_ln = true;                       // LayerNorm in the epilogue of the o / ffn-out GEMMs (BERT_FUSE_LN=0 disables)  // validation kernels forced by env (debug only)
     int t_cap = 0, b_cap = 0;
+    bool gelu_h2 = true;                       // GELU of the FFN-in epilogue in packed half arithmetic (BERT_GELU_H2=0: f32x2 chain)
     int small_t = 256;                         // micro-batches up to this many tokens take the latency path (BERT_SMALL_T)
 
     ~Engine();

@@ -188,6 +188,7 @@ bool Engine::init_devices(const ModelFile & mf) {
     if (const char * e = getenv("BERT_ACT_QUANT")) { if (atoi(e) == 0) fq_type = -1; }
     t_cap = 131072;
     if (const char * e = getenv("BERT_SMALL_T")) small_t = atoi(e);
+    if (const char * e = getenv("BERT_GELU_H2")) gelu_h2 = atoi(e) != 0;
     if (const char * e = getenv("BERT_MICROBATCH_TOKENS")) { int v = atoi(e); if (v >= hp.n_max_tokens) t_cap = v; }
     if (t_cap < hp.n_max_tokens) t_cap = hp.n_max_tokens;
     b_cap = t_cap / 2 < 16384 ? t_cap / 2 : 16384;                // every sentence has >= 2 ids

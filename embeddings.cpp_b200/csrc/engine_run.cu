@@ -93,7 +93,7 @@ bool Engine::forward(Replica & r, const int32_t * d_ids, const int32_t * d_cu, i
             L(KK_LN, launch_ln(r.y, ly.ln_att_g, ly.ln_att_b, T, H, r.x1, fq ? r.x1q : nullptr, fq_type, st), "ln_att");
             end();
         }
-        gemm(&r.tm_x1in, &r.to_mid, r.x1q, ly.ffi, nullptr, nullptr, r.mid, EPI_BIAS | EPI_GELU | (fq ? EPI_FAKEQUANT : 0));
+        gemm(&r.tm_x1in, &r.to_mid, r.x1q, ly.ffi, nullptr, nullptr, r.mid, EPI_BIAS | EPI_GELU | (gelu_h2 ? EPI_GELU_H2 : 0) | (fq ? EPI_FAKEQUANT : 0));
         if (fuse) {
             gemm_ln(&r.tm_mid, r.mid, ly.ffo, r.x1, &r.tr_x1, ly.ln_out_g, ly.ln_out_b, r.x, &r.to_x, &r.to_xq);
         } else {

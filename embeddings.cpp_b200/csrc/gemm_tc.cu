@@ -24,7 +24,10 @@ constexpr int UMMA_K = 16;
 constexpr int kSmemLimit = 232448;                   // 227 KB opt-in limit per CTA
 
 // RES: the epilogue adds a residual (LN implies RES); without it the residual staging goes to the B ring
-template <int BN, int WT, bool LN, bool RES> struct GemmCfg {
+// EPB (fused LayerNorm, short K): the epilogue chain (residual load -> pass 1 -> statistics exchange -> pass 2 ->
+// stores) is longer than the mainloop of a tile, so smem goes to the epilogue instead of the rings: the q8 twin
+// gets its own staging buffer and the residual box of the NEXT tile is fetched while this tile is normalised.
+template <int BN, int WT, bool LN, bool RES, bool EPB = false> struct GemmCfg {
     static constexpr bool kQ4      = WT != W_F16;
     static constexpr int kBHalf    = BN / 2;                 // B rows this CTA supplies
     static constexpr int kABytes   = BM * BK * 2;
@@ -36,6 +39,7 @@ template <int BN, int WT, bool LN, bool RES> struct GemmCfg {
     static constexpr int kAccStride = BN <= 64 ? 64 : (BN <= 128 ? 128 : 256);
     static constexpr int kOutBytes = 8 * 4096;          // 8 epilogue warps x [32 rows][128 B] staging for TMA stores
     static constexpr int kResBytes = RES ? 8 * 4096 : 0; // same geometry, residual boxes prefetched by TMA
+    static constexpr int kTwinBytes = (LN && EPB) ? 8 * 4096 : 0;   // EPB: staging of the q8 twin (otherwise it shares the residual buffer)
     static constexpr int kBiasBytes = LN ? 0 : 8 * 256; // per warp: the 64 bias values of its current box
     // fused LayerNorm: per-row partial statistics of up to 4 pairs x 2 warps, double-buffered, plus the
     // CTA's 256-column slices of bias / gamma / beta
@@ -43,12 +47,12 @@ template <int BN, int WT, bool LN, bool RES> struct GemmCfg {
     static constexpr int kLnStatBytes = LN ? 2 * kLnMaxPairs * 2 * BM * 8 : 0;
     static constexpr int kLnParamBytes = LN ? 3 * BN * 4 : 0;
     static constexpr int kBarBytes = 512;
-    static constexpr int kFixed = kOutBytes + kResBytes + kBiasBytes + kLnStatBytes + kLnParamBytes + 1024 /*align slack*/ + kBarBytes;
+    static constexpr int kFixed = kOutBytes + kResBytes + kTwinBytes + kBiasBytes + kLnStatBytes + kLnParamBytes + 1024 /*align slack*/ + kBarBytes;
     // fp16 weights: A and B travel together through one ring.  q4 weights: A needs TMA-latency depth,
     // the dequantised B only a short ring (it is produced from smem), the 4-bit ring hides L2 latency.
     static constexpr int kFitF16   = (kSmemLimit - kFixed) / (kABytes + kBBytes);
-    static constexpr int kSA       = kQ4 ? (LN ? 4 : 5) : (kFitF16 > 6 ? 6 : kFitF16);
-    static constexpr int kSB       = kQ4 ? (RES ? 3 : (BN > 192 ? 5 : 6)) : kSA;
+    static constexpr int kSA       = kQ4 ? (LN ? (EPB ? 3 : 4) : 5) : (kFitF16 > 6 ? 6 : kFitF16);
+    static constexpr int kSB       = kQ4 ? (RES ? (EPB ? 2 : 3) : (BN > 192 ? 5 : 6)) : kSA;
     // (the 4-bit ring depth stays a multiple of the number of dequant groups, so a slot is always
     // refilled for the same group that drained it)
     static constexpr int kSN       = kQ4 ? 6 : 0;
@@ -87,6 +91,20 @@ __device__ __forceinline__ float2 gelu2_ref_numerics(float2 v) {
     const float2 t = make_float2(tanh_approx(u.x), tanh_approx(u.y));
     const float2 h = __fmul2_rn(f, make_float2(0.5f, 0.5f));
     return round_h2(__ffma2_rn(h, t, h));
+}
+// The same function in packed half arithmetic (EPI_GELU_H2): one F2FP, five HMUL2/HFMA2 and one tanh.approx.f16x2 per
+// PAIR instead of the f32x2 chain with two half round trips.  The input rounding to fp16 is the reference's; the
+// intermediate fp16 roundings add ~1e-3 |x| of absolute error, an order of magnitude below the q8 step the
+// result is quantised to next.
+__device__ __forceinline__ float2 gelu2_half_arith(float2 v) {
+    const __half2 f = __floats2half2_rn(v.x, v.y);
+    const __half2 k1 = __float2half2_rn(0.79788456080286535588f), k2 = __float2half2_rn(0.79788456080286535588f * 0.044715f);
+    const __half2 u = __hmul2(f, __hfma2(__hmul2(f, f), k2, k1));
+    uint32_t ti; const uint32_t ui = *reinterpret_cast<const uint32_t *>(&u);
+    asm("tanh.approx.f16x2 %0, %1;" : "=r"(ti) : "r"(ui));
+    const __half2 t = *reinterpret_cast<const __half2 *>(&ti);
+    const __half2 h = __hmul2(f, __float2half2_rn(0.5f));
+    return __half22float2(__hfma2(h, t, h));
 }
 __device__ __forceinline__ void tma_store_2d(const void * tmap, const void * smem_src, int32_t c0, int32_t c1) {
     asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
@@ -158,13 +176,14 @@ template <bool LN> struct RegBudget {
 };
 
 // Launched with a runtime cluster dimension: 2 (one CTA pair) or, with fused LayerNorm, 2 * N / BN.
-template <int BN, int WT, bool LN, bool RES>
+template <int BN, int WT, bool LN, bool RES, bool EPB>
 __global__ void __launch_bounds__(gemm_threads<WT>(), 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
                const __grid_constant__ CUtensorMap tmap_out2, const GemmParams p) {
     static_assert(RES || !LN, "fused LayerNorm needs the residual path");
-    using Cfg = GemmCfg<BN, WT, LN, RES>;
+    static_assert(LN || !EPB, "EPB is a variant of the fused-LayerNorm epilogue");
+    using Cfg = GemmCfg<BN, WT, LN, RES, EPB>;
     constexpr bool Q4 = Cfg::kQ4;
     constexpr int SA = Cfg::kSA, SB = Cfg::kSB, SN = Cfg::kSN;
     constexpr int NB = BN / 64;                               // 64-column output boxes per tile
@@ -176,7 +195,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     uint8_t * smem_b = smem_a + SA * Cfg::kABytes;            // SB x (BN/2)*128 B
     uint8_t * smem_out = smem_b + SB * Cfg::kBBytes;          // 8 warps x 4 KB staging for TMA stores
     uint8_t * smem_res = smem_out + Cfg::kOutBytes;           // 8 warps x 4 KB residual boxes
-    uint8_t * smem_bias = smem_res + Cfg::kResBytes;          // 8 warps x 64 floats
+    uint8_t * smem_twin = smem_res + Cfg::kResBytes;          // EPB: 8 warps x 4 KB staging of the q8 twin
+    uint8_t * smem_bias = smem_twin + Cfg::kTwinBytes;        // 8 warps x 64 floats
     uint8_t * smem_nib = smem_bias + Cfg::kBiasBytes;         // SN x 4-bit weight stages (q4 only)
     uint8_t * smem_lnstat = smem_nib + SN * Cfg::kNibSlot;    // LN: [2][pairs<=4][2][128] x (mean, M2)
     uint8_t * smem_lnpar = smem_lnstat + Cfg::kLnStatBytes;   // LN: bias | gamma | beta of this CTA's BN columns
@@ -324,6 +344,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         const int row = q * 32 + lane;             // row inside this CTA's 128
         uint8_t * st = smem_out + e * 4096;
         uint8_t * rs = smem_res + e * 4096;
+        uint8_t * tws = EPB ? smem_twin + e * 4096 : rs;      // twin staging (shares the residual buffer unless EPB)
         uint64_t * rbar = rfull + e;
         const float * s_bias = reinterpret_cast<const float *>(smem_lnpar);
         const float * s_gamma = s_bias + BN;
@@ -371,6 +392,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     mbar_expect_tx(rbar, 4096);
                     tma_load_2d(rs, &tmap_res, rbar, nb * BN + (b + 2) * 64, wrow0);
                 }
+                // EPB: the residual buffer is not the twin's staging, so the next tile's first box can travel
+                // while this tile is normalised and stored
+                if (EPB && bi + 1 == NBW && it + 1 < my_tiles && lane == 0) res_load(it + 1);
 #pragma unroll
                 for (int hh = 0; hh < 2; ++hh) {
                     uint32_t r[32];
@@ -482,7 +506,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             __half2 * h = reinterpret_cast<__half2 *>(&u);
 #pragma unroll
                             for (int k = 0; k < 4; ++k) h[k] = __floats2half2_rn(v[i * 4 + k].x, v[i * 4 + k].y);
-                            *reinterpret_cast<uint4 *>(rs + lane * 128 + ((c ^ (lane & 7)) << 4)) = u;
+                            *reinterpret_cast<uint4 *>(tws + lane * 128 + ((c ^ (lane & 7)) << 4)) = u;
                         }
                     }
                 }
@@ -490,13 +514,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 __syncwarp();
                 if (lane == 0) {
                     tma_store_2d(&tmap_out, st, c0, wrow0);
-                    if (fq_on) tma_store_2d(&tmap_out2, rs, c0, wrow0);
+                    if (fq_on) tma_store_2d(&tmap_out2, tws, c0, wrow0);
                     tma_store_commit();
                 }
             }
             // rs doubles as the twin's staging buffer: the next tile's residual may only land once the
             // last store has finished reading it
-            if (it + 1 < my_tiles && lane == 0) { tma_store_wait_read<0>(); res_load(it + 1); }
+            if (!EPB && it + 1 < my_tiles && lane == 0) { tma_store_wait_read<0>(); res_load(it + 1); }
         }
         if (lane == 0) tma_store_wait_all<0>();
       } else {
@@ -579,7 +603,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             v[2 * i + 1] = __fadd2_rn(v[2 * i + 1], make_float2(bb.z, bb.w));
                         }
                     }
-                    if (p.epilogue & EPI_GELU) {
+                    if (p.epilogue & EPI_GELU_H2) {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) v[i] = gelu2_half_arith(v[i]);
+                    } else if (p.epilogue & EPI_GELU) {
 #pragma unroll
                         for (int i = 0; i < 16; ++i) v[i] = gelu2_ref_numerics(v[i]);
                     }
@@ -700,11 +727,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 }
 
 // Persistent grid: as many clusters as the device can keep resident (cached per device and cluster size).
-template <int BN, int WT, bool LN, bool RES>
+template <int BN, int WT, bool LN, bool RES, bool EPB>
 static int max_clusters(int device, int num_sms, int csize) {
     static int cached[64][9] = {};
     if (device >= 0 && device < 64 && cached[device][csize] > 0) return cached[device][csize];
-    using Cfg = GemmCfg<BN, WT, LN, RES>;
+    using Cfg = GemmCfg<BN, WT, LN, RES, EPB>;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned) (num_sms / csize * csize));
     cfg.blockDim = dim3(gemm_threads<WT>());
@@ -714,7 +741,7 @@ static int max_clusters(int device, int num_sms, int csize) {
     at[0].val.clusterDim.x = (unsigned) csize; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
     int n = 0;
-    if (cudaOccupancyMaxActiveClusters(&n, gemm_tc_kernel<BN, WT, LN, RES>, &cfg) != cudaSuccess || n <= 0) {
+    if (cudaOccupancyMaxActiveClusters(&n, gemm_tc_kernel<BN, WT, LN, RES, EPB>, &cfg) != cudaSuccess || n <= 0) {
         cudaGetLastError();
         n = csize == 2 ? num_sms / 2 : 1;
     }
@@ -723,11 +750,11 @@ static int max_clusters(int device, int num_sms, int csize) {
     return n;
 }
 
-template <int BN, int WT, bool LN, bool RES>
+template <int BN, int WT, bool LN, bool RES, bool EPB = false>
 static cudaError_t launch_one(const GemmArgs & g, int num_sms, cudaStream_t st) {
-    using Cfg = GemmCfg<BN, WT, LN, RES>;
+    using Cfg = GemmCfg<BN, WT, LN, RES, EPB>;
     static_assert(Cfg::kSA >= 3, "pipeline too shallow");
-    auto kern = gemm_tc_kernel<BN, WT, LN, RES>;
+    auto kern = gemm_tc_kernel<BN, WT, LN, RES, EPB>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
     if (e != cudaSuccess) return e;
     int device = 0;
@@ -737,7 +764,7 @@ static cudaError_t launch_one(const GemmArgs & g, int num_sms, cudaStream_t st) 
     const int num_m = (g.M + 2 * BM - 1) / (2 * BM), num_n = w.N / BN;
     const int csize = LN ? 2 * num_n : 2;                 // CTAs per cluster
     const int units = LN ? num_m : num_m * num_n;         // stripes or tiles to hand out
-    const int ncl_max = max_clusters<BN, WT, LN, RES>(device, num_sms, csize);
+    const int ncl_max = max_clusters<BN, WT, LN, RES, EPB>(device, num_sms, csize);
     const int ncl = units < ncl_max ? units : ncl_max;
     if (ncl <= 0) return cudaSuccess;
     if ((g.epilogue & EPI_RESIDUAL) && !g.tmap_res) return cudaErrorInvalidValue;
@@ -778,14 +805,19 @@ cudaError_t launch_gemm_tc(const GemmArgs & g, int num_sms, cudaStream_t st) {
     if (bn == 0 || w.K % BK != 0) return cudaErrorInvalidValue;
     if (g.epilogue & EPI_LN) {
         if (!gemm_ln_fusable(w) || (g.epilogue & EPI_GELU) || !(g.epilogue & EPI_RESIDUAL) || !(g.epilogue & EPI_BIAS)) return cudaErrorInvalidValue;
-#define DISPATCH_LN(BN_)                                                                        \
+        // short K (the attention-output GEMM): the epilogue chain outlasts the mainloop -> EPB variant
+        // (BERT_LN_EPB: 0 never, 1 when K <= 1024 (default), 2 always)
+        static const int epb_mode = [] { const char * e = getenv("BERT_LN_EPB"); return e ? atoi(e) : 1; }();
+        const bool epb = epb_mode == 2 || (epb_mode == 1 && w.K <= 1024);
+#define DISPATCH_LN(BN_, EPB_)                                                                  \
         switch (w.type) {                                                                       \
-            case W_F16:  return launch_one<BN_, W_F16, true, true>(g, num_sms, st);              \
-            case W_Q4_0: return launch_one<BN_, W_Q4_0, true, true>(g, num_sms, st);             \
-            case W_Q4_1: return launch_one<BN_, W_Q4_1, true, true>(g, num_sms, st);             \
+            case W_F16:  return launch_one<BN_, W_F16, true, true, EPB_>(g, num_sms, st);        \
+            case W_Q4_0: return launch_one<BN_, W_Q4_0, true, true, EPB_>(g, num_sms, st);       \
+            case W_Q4_1: return launch_one<BN_, W_Q4_1, true, true, EPB_>(g, num_sms, st);       \
             default: return cudaErrorInvalidValue;                                              \
         }
-        if (bn == 256) { DISPATCH_LN(256) } else { DISPATCH_LN(128) }
+        if (bn == 256) { if (epb) { DISPATCH_LN(256, true) } else { DISPATCH_LN(256, false) } }
+        else { if (epb) { DISPATCH_LN(128, true) } else { DISPATCH_LN(128, false) } }
 #undef DISPATCH_LN
     }
 #define DISPATCH_WT(BN_)                                                                        \

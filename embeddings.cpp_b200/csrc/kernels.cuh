@@ -14,7 +14,8 @@ namespace b200 {
 enum WType : int { W_F32 = 0, W_F16 = 1, W_Q4_0 = 2, W_Q4_1 = 3 };
 
 // epilogue flags of the GEMM
-enum : int { EPI_BIAS = 1, EPI_GELU = 2, EPI_RESIDUAL = 4, EPI_FAKEQUANT = 8, EPI_LN = 16 };
+// (EPI_GELU_H2, together with EPI_GELU: the tcgen05 kernel evaluates GELU in packed half arithmetic)
+enum : int { EPI_BIAS = 1, EPI_GELU = 2, EPI_RESIDUAL = 4, EPI_FAKEQUANT = 8, EPI_LN = 16, EPI_GELU_H2 = 32 };
 
 // A dense weight matrix W[N][K] (K contiguous = the file's ne0, reference bert.cpp:611-623)
 // resident in HBM in its GEMM-ready form:

@@ -45,6 +45,7 @@ def models(pkg):
     (1, 128, 64, 64, 0), (1, 300, 192, 256, 5), (1, 1000, 768, 768, 3), (1, 4096, 3072, 768, 3),
     (2, 128, 64, 64, 0), (2, 300, 256, 256, 1), (2, 1000, 768, 768, 7), (2, 4096, 768, 3072, 5),
     (3, 128, 128, 128, 1), (3, 2048, 1024, 512, 7), (2, 131, 2304, 768, 1), (3, 77, 1152, 384, 1),
+    (1, 1000, 768, 768, 35), (2, 900, 3072, 768, 35),          # 32 = EPI_GELU_H2: GELU in packed half arithmetic
 ])
 def test_tcgen05_gemm_matches_simt_reference(pkg, wt, M, N, K, epi):
     rc, err, ref = pkg.selftest_gemm(M, N, K, wt, epi, seed=M + N)
@@ -52,7 +53,8 @@ def test_tcgen05_gemm_matches_simt_reference(pkg, wt, M, N, K, epi):
     assert np.isfinite(err) and err <= 4e-3 * max(ref, 1.0), (err, ref)       # fp16 output rounding
 
 
-@pytest.mark.parametrize("wt,M,N,K,epi", [(2, 515, 192, 384, 11), (3, 777, 1024, 512, 15), (2, 640, 3072, 768, 11)])
+@pytest.mark.parametrize("wt,M,N,K,epi", [(2, 515, 192, 384, 11), (3, 777, 1024, 512, 15), (2, 640, 3072, 768, 11),
+                                           (2, 640, 3072, 768, 43), (3, 515, 1536, 384, 43)])
 def test_tcgen05_gemm_with_q8_fakequant_epilogue(pkg, wt, M, N, K, epi):
     rc, err, ref = pkg.selftest_gemm(M, N, K, wt, epi, seed=3)
     assert rc == 0

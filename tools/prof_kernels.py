@@ -1,6 +1,6 @@
 """Small driver for `ncu --set full`: one launch of each hot kernel at the bge-base shapes
 (q4_0 GEMMs at M tokens, tcgen05 attention over 64 x 512-token sentences).
-    python tools/prof_kernels.py [M [names]]     names: comma list of qkv,o,ffn_in,ffn_out,o_ln,ffn_out_ln,attn"""
+    python tools/prof_kernels.py [M [names]]     names: comma list of qkv,o,ffn_in,ffn_in_h2,ffn_out,o_ln,ffn_out_ln,attn"""
 import os
 import sys
 
@@ -14,7 +14,7 @@ H, I = 768, 3072
 names = sys.argv[2].split(",") if len(sys.argv) > 2 else ["qkv", "o", "ffn_in", "ffn_out", "attn"]
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 1
 shapes = {"qkv": (3 * H, H, 1), "o": (H, H, 5), "ffn_in": (I, H, 11), "ffn_out": (H, I, 5),
-          "o_ln": (H, H, 29), "ffn_out_ln": (H, I, 29)}
+          "o_ln": (H, H, 29), "ffn_out_ln": (H, I, 29), "ffn_in_h2": (I, H, 43)}
 for name in names:
     if name == "attn":
         print("attn", pkg.selftest_attention(64, 512, 12, 64, 1))
