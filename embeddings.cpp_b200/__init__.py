@@ -60,6 +60,8 @@ def lib():
     L.bertx_n_devices.argtypes = [vp]
     L.bertx_hparam.restype = c_i32
     L.bertx_hparam.argtypes = [vp, c_i32]
+    L.bertx_set_pooling.restype = c_i32
+    L.bertx_set_pooling.argtypes = [vp, c_i32]
     L.bertx_kernel_launches.restype = c_i64
     L.bertx_kernel_launches.argtypes = [vp]
     L.bertx_tokenize_batch.restype = c_i64
@@ -166,6 +168,13 @@ class BertModel:
     def hparams(self):
         k = ["n_vocab", "n_max_tokens", "n_embd", "n_intermediate", "n_head", "n_layer", "ftype"]
         return {name: self.lib.bertx_hparam(self.ctx, i) for i, name in enumerate(k)}
+
+    def set_pooling(self, mode):
+        """'mean' (reference behaviour) or 'cls' (opt-in extension); returns the previous mode."""
+        prev = self.lib.bertx_set_pooling(self.ctx, {"mean": 0, "cls": 1}[mode])
+        if prev < 0:
+            raise ValueError(mode)
+        return ["mean", "cls"][prev]
 
     def kernel_launches(self):
         return int(self.lib.bertx_kernel_launches(self.ctx))

@@ -309,6 +309,14 @@ int32_t bertx_hparam(struct bert_ctx * ctx, int32_t index) {
 
 int64_t bertx_kernel_launches(struct bert_ctx * ctx) { return ctx->eng.launches.load(); }
 
+int32_t bertx_set_pooling(struct bert_ctx * ctx, int32_t mode) {
+    if (!ctx || (mode != 0 && mode != 1)) return -1;
+    std::lock_guard<std::mutex> lk(ctx->eng.mu);
+    const int32_t prev = ctx->eng.pooling;
+    ctx->eng.pooling = mode;
+    return prev;
+}
+
 int64_t bertx_tokenize_batch(struct bert_ctx * ctx, int32_t n_threads, int32_t n_inputs, const char ** texts,
                              bert_vocab_id * tokens_out, int64_t cap, int32_t * n_tokens_out) {
     try {

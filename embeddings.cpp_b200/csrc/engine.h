@@ -86,6 +86,7 @@ struct Engine {
     bool fuse_ln = true;                       // LayerNorm in the epilogue of the o / ffn-out GEMMs (BERT_FUSE_LN=0 disables)  // validation kernels forced by env (debug only)
     int t_cap = 0, b_cap = 0;
     bool gelu_h2 = true;                       // GELU of the FFN-in epilogue in packed half arithmetic (BERT_GELU_H2=0: f32x2 chain)
+    int pooling = 0;                           // 0 = masked mean over all valid tokens (the reference, bert.cpp:1087-1089); 1 = [CLS] row (opt-in: BERT_POOLING=cls / bertx_set_pooling)
     int small_t = 256;                         // micro-batches up to this many tokens take the latency path (BERT_SMALL_T)
 
     ~Engine();

@@ -104,7 +104,7 @@ bool Engine::forward(Replica & r, const int32_t * d_ids, const int32_t * d_cu, i
         }
     }
     begin(KK_POOL);
-    L(KK_POOL, launch_pool_norm(r.x, d_cu, n_sent, H, d_out, st), "pool_norm");
+    L(KK_POOL, launch_pool_norm(r.x, d_cu, n_sent, H, d_out, pooling, st), "pool_norm");
     end();
     return L.ok;
 }

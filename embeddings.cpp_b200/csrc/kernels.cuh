@@ -98,7 +98,7 @@ cudaError_t launch_attention_ref(const __half * qkv, const int32_t * cu_seqlens,
 
 // K4: masked mean over the sentence's tokens + L2 normalise -> f32 [n_sent][H]
 cudaError_t launch_pool_norm(const __half * x, const int32_t * cu_seqlens, int n_sent, int H,
-                             float * out, cudaStream_t st);
+                             float * out, int cls, cudaStream_t st);
 
 // Every kernel of the forward is launched through this helper: with programmatic dependent launch (PDL) the
 // next kernel's launch latency and prologue (barrier init, TMEM allocation, descriptor prefetch) overlap the tail

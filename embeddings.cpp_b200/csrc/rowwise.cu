@@ -199,12 +199,13 @@ embed_ln_kernel(const DevTable word, const float * __restrict__ postype,
 // flight per SM for a grid of only n_sent CTAs; the stripe sums are combined in a fixed order (deterministic).
 constexpr int POOL_THREADS = 1024;
 __global__ void __launch_bounds__(POOL_THREADS)
-pool_norm_kernel(const __half * __restrict__ x, const int32_t * __restrict__ cu, int H, float * __restrict__ out) {
+pool_norm_kernel(const __half * __restrict__ x, const int32_t * __restrict__ cu, int H, float * __restrict__ out, int cls) {
     extern __shared__ float sm[];                       // [stripes][H] then reduction scratch
     pdl_launch_dependents();
     pdl_wait();
     const int sent = blockIdx.x;
-    const int t0 = cu[sent], len = cu[sent + 1] - t0;
+    // CLS pooling (opt-in extension; the reference only has the masked mean): the sentence is its [CLS] row
+    const int t0 = cu[sent], len = cls ? 1 : cu[sent + 1] - t0;
     const int ncol = H / 8;
     const int stripes = POOL_THREADS / ncol;
     const int c = threadIdx.x % ncol, sidx = threadIdx.x / ncol;
@@ -280,12 +281,12 @@ cudaError_t launch_ln(const __half * x, const float * gamma, const float * beta,
 }
 
 cudaError_t launch_pool_norm(const __half * x, const int32_t * cu_seqlens, int n_sent, int H,
-                             float * out, cudaStream_t st) {
+                             float * out, int cls, cudaStream_t st) {
     if (n_sent <= 0) return cudaSuccess;
     if (H > 2 * POOL_THREADS) return cudaErrorInvalidValue;
     const int stripes = POOL_THREADS / (H / 8);
     const size_t smem = (size_t) (stripes > 0 ? stripes : 1) * H * sizeof(float);
-    return launch_pdl(pool_norm_kernel, dim3(n_sent), dim3(POOL_THREADS), smem, st, x, cu_seqlens, H, out);
+    return launch_pdl(pool_norm_kernel, dim3(n_sent), dim3(POOL_THREADS), smem, st, x, cu_seqlens, H, out, cls);
 }
 
 }  // namespace b200

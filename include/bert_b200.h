@@ -52,6 +52,11 @@ BERT_API int32_t bertx_run_staged(struct bert_ctx * ctx, int32_t dev, int32_t re
 BERT_API int32_t bertx_profile_staged(struct bert_ctx * ctx, int32_t dev,
                                       float * ms_by_kind, int64_t * launches_by_kind);
 
+/* Pooling of the final hidden states: 0 = masked mean over all valid tokens (the reference's only mode,
+ * bert.cpp:1087-1089; default), 1 = the [CLS] row (what the BGE model cards specify; opt-in extension, also
+ * BERT_POOLING=cls at load).  Both are followed by the L2 normalisation.  Returns the previous mode, -1 on a bad argument. */
+BERT_API int32_t bertx_set_pooling(struct bert_ctx * ctx, int32_t mode);
+
 /* Kernel launches issued by this context since load (all devices). */
 BERT_API int64_t bertx_kernel_launches(struct bert_ctx * ctx);
 

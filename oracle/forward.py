@@ -77,8 +77,10 @@ class OracleModel:
         y = x @ w.T
         return (y + self.w[bname]).astype(F32)
 
-    def forward(self, batch_tokens, exact_activations=False, return_hidden=False):
-        """batch_tokens: list of lists of ids.  Returns [B, n_embd] float32."""
+    def forward(self, batch_tokens, exact_activations=False, return_hidden=False, pooling="mean"):
+        """batch_tokens: list of lists of ids.  Returns [B, n_embd] float32.
+        pooling="cls" is NOT in the reference (it only has the masked mean, bert.cpp:1087-1089): it checks the
+        opt-in [CLS] extension of the CUDA path -- same hidden states, row 0 instead of the mean."""
         hp = self.hp
         ex = exact_activations
         H, nh = hp.n_embd, hp.n_head
@@ -130,7 +132,7 @@ class OracleModel:
             o = self._linear(h, p + "output.dense.weight", p + "output.dense.bias", ex)
             x = layer_norm((a + o).astype(F32), W[p + "output.LayerNorm.weight"],
                            W[p + "output.LayerNorm.bias"]).reshape(B, L, H)
-        pooled = np.einsum("blh,bl->bh", x, wsum).astype(F32)
+        pooled = x[:, 0, :].astype(F32) if pooling == "cls" else np.einsum("blh,bl->bh", x, wsum).astype(F32)
         norm = np.sqrt((pooled * pooled).sum(axis=-1, keepdims=True)).astype(F32)
         out = (pooled / norm).astype(F32)
         if return_hidden:

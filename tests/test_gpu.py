@@ -145,6 +145,29 @@ def test_zero_layer_model(pkg):
         m.close()
 
 
+@pytest.mark.parametrize("ft", ["f16", "q4_0"])
+def test_cls_pooling_extension(pkg, ft):
+    """Opt-in [CLS] pooling (bertx_set_pooling / BERT_POOLING=cls; north_star (e)).  The reference has
+    no such mode, so the check is the numpy restatement with row 0 in place of the masked mean; switching back
+    restores the reference's mean bit for bit."""
+    model = synth.model_path("tiny-d64", ft)
+    mf = fileformat.read_model(model)
+    m = pkg.BertModel(model)
+    om = forward.OracleModel(mf)
+    toks = [[101, 300, 301, 302, 102], [101, 102], [101] + list(range(200, 330)) + [102]]
+    mean0 = m.forward_tokens(toks)
+    assert m.set_pooling("cls") == "mean"
+    got = m.forward_tokens(toks)
+    want = om.forward(toks, pooling="cls")
+    cos, err = cos_and_maxabs(got, want)
+    assert cos >= COS_MIN and err <= MAX_ABS[ft], (cos, err)
+    assert np.allclose(np.linalg.norm(got, axis=1), 1.0, atol=1e-4)
+    assert np.abs(got - mean0).max() > 1e-3                      # it really is a different pooling
+    assert m.set_pooling("mean") == "cls"
+    assert np.array_equal(m.forward_tokens(toks), mean0)
+    m.close()
+
+
 def test_staged_job_equals_encode_and_multi_microbatch(pkg):
     """Device-resident path (bench `value`) gives the same embeddings as bert_encode_batch,
     also when the job is cut into several micro-batches."""
@@ -178,6 +201,7 @@ def test_staged_job_equals_encode_and_multi_microbatch(pkg):
     ("bge-small-en-v1.5", "f16", 16, 100, 128),
     ("bge-small-zh-v1.5", "q4_1", 24, 2, 256),
     ("bge-base-en-v1.5", "q4_0", 6, 200, 512),
+    ("bge-large-en-v1.5", "q4_0", 4, 120, 256),
 ])
 def test_named_model_shapes_against_live_reference(pkg, shape, ft, n, lo, hi):
     """BASELINE.json configs at the named shapes (synthetic weights), live compiled reference."""
