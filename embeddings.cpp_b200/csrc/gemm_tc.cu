@@ -28,7 +28,7 @@ constexpr int kSmemLimit = 232448;                   // 227 KB opt-in limit per 
 // stores) is longer than the mainloop of a tile, so smem goes to the epilogue instead of the rings: the q8 twin
 // gets its own staging buffer and the residual box of the NEXT tile is fetched while this tile is normalised.
 #ifndef BERT_EPI_LD2
-#define BERT_EPI_LD2 0
+#define BERT_EPI_LD2 1       // both 32-column halves of an epilogue box loaded from TMEM before the single wait (QKV 0.359 -> 0.355 ms at 131072 tokens)
 #endif
 template <int BN, int WT, bool LN, bool RES, bool EPB = false> struct GemmCfg {
     static constexpr bool kQ4      = WT != W_F16;
