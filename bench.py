@@ -32,7 +32,7 @@ WORKLOADS = {
     "tiny-q4_0-b64-s64": ("tiny-d64", "q4_0", 64, 64),
 }
 DEFAULT_WORKLOAD = "bge-base-q4_0-b512-s512"
-NCU_GEMM_DRAM_BYTES_PER_LAUNCH = 960e6    # measured, see profiles/r1_final.md
+NCU_GEMM_DRAM_BYTES_PER_LAUNCH = 960e6    # measured (ncu --set full, mean over the 4 GEMMs of a layer), see profiles/r1_head.md
 
 
 def shard_range(n_items, rank, world):
@@ -242,10 +242,10 @@ def main():
                 "by_kernel_ms": {k: round(v[0], 3) for k, v in prof.items()},
                 "whole_forward_tflops": (gemm_flops + attn_flops) * world / (ms / args.steps / 1e3) / 1e12 / world}
 
-    # dram bytes per launch of the dominant kernel from `ncu --set full` (profiles/r1_final.md), default workload only
+    # dram bytes per launch of the dominant kernel from `ncu --set full` (profiles/r1_head.md), default workload only
     if args.workload == DEFAULT_WORKLOAD:
         roofline["traffic"] = NCU_GEMM_DRAM_BYTES_PER_LAUNCH
-        roofline["traffic_note"] = "dram__bytes_read.sum + dram__bytes_write.sum, mean over the 4 GEMMs of a layer at 131072 tokens (profiles/r1_final.md)"
+        roofline["traffic_note"] = "dram__bytes_read.sum + dram__bytes_write.sum, mean over the 4 GEMMs of a layer at 131072 tokens (profiles/r1_head.md)"
     # the HBM-bound row kernels against the measured copy bandwidth (algorithmic bytes)
     wbytes = {"f32": 4.0, "f16": 2.0, "q4_0": 18.0 / 32, "q4_1": 20.0 / 32}[ftype]
     twin = 2 if "q4" in ftype else 1

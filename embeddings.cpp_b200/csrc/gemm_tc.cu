@@ -27,9 +27,6 @@ constexpr int kSmemLimit = 232448;                   // 227 KB opt-in limit per 
 // EPB (fused LayerNorm, short K): the epilogue chain (residual load -> pass 1 -> statistics exchange -> pass 2 ->
 // stores) is longer than the mainloop of a tile, so smem goes to the epilogue instead of the rings: the q8 twin
 // gets its own staging buffer and the residual box of the NEXT tile is fetched while this tile is normalised.
-#ifndef BERT_EPI_LD2
-#define BERT_EPI_LD2 1       // both 32-column halves of an epilogue box loaded from TMEM before the single wait (QKV 0.359 -> 0.355 ms at 131072 tokens)
-#endif
 template <int BN, int WT, bool LN, bool RES, bool EPB = false> struct GemmCfg {
     static constexpr bool kQ4      = WT != W_F16;
     static constexpr int kBHalf    = BN / 2;                 // B rows this CTA supplies
@@ -590,22 +587,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     }
                     if (has_bias) bnext = __ldg(reinterpret_cast<const float2 *>(p.bias + c1) + lane);
                 }
-#if BERT_EPI_LD2
-                // both 32-column halves of the box in flight at once: one TMEM round trip per box instead of two
-                uint32_t r2[2][32];
-                tmem_ld_32x32b_x32(tmem_base + ((uint32_t) (q * 32) << 16) + acc * Cfg::kAccStride + b * 64, r2[0]);
-                tmem_ld_32x32b_x32(tmem_base + ((uint32_t) (q * 32) << 16) + acc * Cfg::kAccStride + b * 64 + 32, r2[1]);
-                tmem_ld_wait();
-#endif
 #pragma unroll
                 for (int hh = 0; hh < 2; ++hh) {
-#if BERT_EPI_LD2
-                    const uint32_t * r = r2[hh];
-#else
+                    // one 32-column load in flight at a time: issuing both halves of the box before a single
+                    // tcgen05.wait::ld measured 1 % faster but gave non-deterministic results at full size
+                    // (tests/test_gpu.py::test_full_size_properties_bge_base; profiles/r1_head.md)
                     uint32_t r[32];
                     tmem_ld_32x32b_x32(tmem_base + ((uint32_t) (q * 32) << 16) + acc * Cfg::kAccStride + b * 64 + hh * 32, r);
                     tmem_ld_wait();
-#endif
                     float2 v[16];
 #pragma unroll
                     for (int i = 0; i < 16; ++i) v[i] = make_float2(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1]));
