@@ -108,6 +108,9 @@ __device__ __forceinline__ float2 ex2_poly2(float2 x) {
     return make_float2(__uint_as_float(__float_as_uint(q.x) + (__float_as_uint(t.x) << 23)),
                        __uint_as_float(__float_as_uint(q.y) + (__float_as_uint(t.y) << 23)));
 }
+#ifndef BERT_ATTN_LDW
+#define BERT_ATTN_LDW 0
+#endif
 #ifndef BERT_ATTN_POLY_EVERY
 #define BERT_ATTN_POLY_EVERY 4
 #endif
@@ -255,9 +258,13 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                 tc_fence_after_sync();
                 const uint32_t s_addr = lane_base + TM_S + (gb & 1) * 64;
                 uint32_t r0[32], r1[32];
+#if BERT_ATTN_LDW
+                tmem_ld_32x32b_x32x2_wait(s_addr, r0, s_addr + 32, r1);
+#else
                 tmem_ld_32x32b_x32(s_addr, r0);
                 tmem_ld_32x32b_x32(s_addr + 32, r1);
                 tmem_ld_wait();
+#endif
                 float s[64];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) { s[j] = __uint_as_float(r0[j]); s[32 + j] = __uint_as_float(r1[j]); }
@@ -316,9 +323,13 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
             mbar_wait(&pv_done[(g - 1) & 1], ((g - 1) >> 1) & 1);
             tc_fence_after_sync();
             uint32_t o0[32], o1[32];
+#if BERT_ATTN_LDW
+            tmem_ld_32x32b_x32x2_wait(lane_base + TM_O, o0, lane_base + TM_O + 32, o1);
+#else
             tmem_ld_32x32b_x32(lane_base + TM_O, o0);
             tmem_ld_32x32b_x32(lane_base + TM_O + 32, o1);
             tmem_ld_wait();
+#endif
             tc_fence_before_sync();
             __syncwarp();
             if (lane == 0) mbar_arrive(o_free);

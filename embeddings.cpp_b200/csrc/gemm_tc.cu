@@ -589,9 +589,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 }
 #pragma unroll
                 for (int hh = 0; hh < 2; ++hh) {
-                    // one 32-column load in flight at a time: issuing both halves of the box before a single
-                    // tcgen05.wait::ld measured 1 % faster but gave non-deterministic results at full size
-                    // (tests/test_gpu.py::test_full_size_properties_bge_base; profiles/r1_head.md)
+                    // one 32-column load in flight at a time: loading both halves of the box up front (two loads + one
+                    // tcgen05.wait::ld, also as a single asm statement) measured 1 % faster but gave NON-DETERMINISTIC
+                    // results at full size (tests/test_gpu.py::test_full_size_properties_bge_base failed 7 of 7 runs,
+                    // this form 0 of 7; kernel self-tests pass either way).  Root cause open: profiles/r1_head.md
                     uint32_t r[32];
                     tmem_ld_32x32b_x32(tmem_base + ((uint32_t) (q * 32) << 16) + acc * Cfg::kAccStride + b * 64 + hh * 32, r);
                     tmem_ld_wait();
