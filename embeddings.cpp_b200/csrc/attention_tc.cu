@@ -33,9 +33,11 @@ constexpr int kQBytes = AQ * AD * 2;          // 16 KB
 constexpr int kKVBytes = AK * AD * 2;         // 8 KB each for K and V
 constexpr int Q_STAGES = 1;
 constexpr int kOutStage = 4 * 4096;            // per softmax warp: [32 rows][128 B] staging for coalesced output rows
-constexpr int kAttSmem = Q_STAGES * kQBytes + KV_STAGES * 2 * kKVBytes + kOutStage + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int kOnesBytes = 16 * 128;            // 16 rows x 64 fp16 of 1.0: K-major B operand (N = 16) of the row-sum MMA
+constexpr int kAttSmem = Q_STAGES * kQBytes + KV_STAGES * 2 * kKVBytes + kOutStage + kOnesBytes + 1024 /*align*/ + 256 /*barriers*/;
 constexpr uint32_t TM_S = 0;       // S buffers at columns 0 and 64 (P aliases the first 32 columns of each)
 constexpr uint32_t TM_O = 128;     // O accumulator: 64 columns
+[[maybe_unused]] constexpr uint32_t TM_L = 192;     // row sums (BERT_ATTN_MMASUM): 16 identical columns
 constexpr uint32_t TM_COLS = 256;
 constexpr float kRescaleThreshold = 8.f;      // log2 units
 
@@ -108,6 +110,11 @@ __device__ __forceinline__ float2 ex2_poly2(float2 x) {
     return make_float2(__uint_as_float(__float_as_uint(q.x) + (__float_as_uint(t.x) << 23)),
                        __uint_as_float(__float_as_uint(q.y) + (__float_as_uint(t.y) << 23)));
 }
+// BERT_ATTN_MMASUM=1: the softmax row sums come out of the tensor core (P x ones tile -> 16 extra TMEM columns next to O)
+// instead of 32 FADD2 per block and warp; the sum is then over the fp16-rounded P, i.e. exactly what multiplies V.
+#ifndef BERT_ATTN_MMASUM
+#define BERT_ATTN_MMASUM 1
+#endif
 #ifndef BERT_ATTN_LDW
 #define BERT_ATTN_LDW 0
 #endif
@@ -131,7 +138,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     uint8_t * smem_k = smem + Q_STAGES * kQBytes;                    // KV_STAGES x 8 KB
     uint8_t * smem_v = smem_k + KV_STAGES * kKVBytes;                // KV_STAGES x 8 KB
     uint8_t * smem_o = smem_v + KV_STAGES * kKVBytes;                // 4 x 4 KB output staging
-    uint64_t * bars = (uint64_t *) (smem_o + kOutStage);
+    uint8_t * smem_ones = smem_o + kOutStage;                        // 2 KB of fp16 1.0
+    uint64_t * bars = (uint64_t *) (smem_ones + kOnesBytes);
     uint64_t * q_full = bars;                   // [Q_STAGES]
     uint64_t * q_empty = bars + Q_STAGES;       // [Q_STAGES]
     uint64_t * kv_full = q_empty + Q_STAGES;    // [KV_STAGES]
@@ -156,6 +164,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         fence_mbar_init();
     }
     if (warp == 1) { tmem_alloc(tmem_slot, TM_COLS); tmem_relinquish(); }
+#if BERT_ATTN_MMASUM
+    for (int i = threadIdx.x; i < kOnesBytes / 4; i += ATT_TC_THREADS) reinterpret_cast<uint32_t *>(smem_ones)[i] = 0x3C003C00u;
+    fence_proxy_async_smem();
+#endif
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
@@ -191,6 +203,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         // ------------------------------------------------------------ MMA issuer
         constexpr uint32_t idesc_s = umma_idesc_f16(AQ, AK);            // Q (K-major) x K (K-major)
         constexpr uint32_t idesc_o = umma_idesc_f16(AQ, AD, 1);         // P (TMEM) x V (MN-major)
+#if BERT_ATTN_MMASUM
+        constexpr uint32_t idesc_l = umma_idesc_f16(AQ, 16);            // P (TMEM) x ones (K-major, N = 16)
+        const uint64_t onesdesc = umma_smem_desc_sw128(smem_u32(smem_ones));
+#endif
         uint32_t g = 0, item_n = 0;                                     // g: running key-block counter
         ItemWalk walk(p, blockIdx.x, gridDim.x, total_items);
         while (walk.advance(p)) {
@@ -231,6 +247,11 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                             umma_f16_ts(tmem_base + TM_O, a_tmem + 8 * k, vdesc + (uint64_t) (128 * k), idesc_o,
                                         (b > 1 || k > 0) ? 1u : 0u);
                         }
+#if BERT_ATTN_MMASUM
+#pragma unroll
+                        for (int k = 0; k < AK / 16; ++k)
+                            umma_f16_ts(tmem_base + TM_L, a_tmem + 8 * k, onesdesc + 2 * k, idesc_l, (b > 1 || k > 0) ? 1u : 0u);
+#endif
                         umma_commit(&kv_empty[st]);
                         umma_commit(&pv_done[gp & 1]);
                     }
@@ -283,7 +304,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                 // move the reference max only on the first block or when it is exceeded by > 2^8
                 const bool need = mx > m_ref + kRescaleThreshold;       // always true on the first block (m_ref = -inf)
                 float factor = 1.f;
-                if (need) { factor = ex2f(m_ref - mx); m_ref = mx; l *= factor; }
+                if (need) { factor = ex2f(m_ref - mx); m_ref = mx; l *= factor; }   // (l unused with BERT_ATTN_MMASUM)
                 if (b >= 1 && __any_sync(0xffffffffu, need)) {
                     // rare: the previous block's P V must be in the accumulator before it may be rescaled.
                     // The wait is only paid here: S_b complete (s_full above) implies P V of block b-2 complete
@@ -291,7 +312,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                     mbar_wait(&pv_done[(gb - 1) & 1], ((gb - 1) >> 1) & 1);
                     tc_fence_after_sync();
 #pragma unroll 1
-                    for (int hh = 0; hh < 2; ++hh) {          // 32 columns at a time: keep this path lean in registers
+                    for (int hh = 0; hh < (BERT_ATTN_MMASUM ? 3 : 2); ++hh) {   // 32 columns at a time (third pass: the row sums at TM_L = TM_O + 64)
                         uint32_t o[32];
                         tmem_ld_32x32b_x32(lane_base + TM_O + hh * 32, o);
                         tmem_ld_wait();
@@ -308,7 +329,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                     const float2 x = __ffma2_rn(make_float2(s[2 * j], s[2 * j + 1]), sc2, nm2);
                     const float2 e = (kPolyEvery > 0 && j % (kPolyEvery > 0 ? kPolyEvery : 1) == kPolyEvery - 1)
                                          ? ex2_poly2(x) : make_float2(ex2f(x.x), ex2f(x.y));
+#if !BERT_ATTN_MMASUM
                     sum[j & 1] = __fadd2_rn(sum[j & 1], e);
+#endif
                     pk[j] = pack_h2(e.x, e.y);
                 }
                 l += (sum[0].x + sum[0].y) + (sum[1].x + sum[1].y);
@@ -322,6 +345,14 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
             // ---- finalize: O / l, optional q8 fake-quant per 32-wide block, fp16 store of valid rows
             mbar_wait(&pv_done[(g - 1) & 1], ((g - 1) >> 1) & 1);
             tc_fence_after_sync();
+#if BERT_ATTN_MMASUM
+            {
+                uint32_t lsum;
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];\n\ttcgen05.wait::ld.sync.aligned;"
+                             : "=r"(lsum) : "r"(lane_base + TM_L) : "memory");
+                l = __uint_as_float(lsum);
+            }
+#endif
             uint32_t o0[32], o1[32];
 #if BERT_ATTN_LDW
             tmem_ld_32x32b_x32x2_wait(lane_base + TM_O, o0, lane_base + TM_O + 32, o1);
