@@ -115,6 +115,13 @@ __device__ __forceinline__ float2 ex2_poly2(float2 x) {
 #ifndef BERT_ATTN_MMASUM
 #define BERT_ATTN_MMASUM 1
 #endif
+// BERT_ATTN_SPEC=1 (needs BERT_ATTN_MMASUM): exponentials against the current reference max, row max checked afterwards
+#ifndef BERT_ATTN_SPEC
+#define BERT_ATTN_SPEC 0
+#endif
+#if BERT_ATTN_SPEC && !BERT_ATTN_MMASUM
+#error "BERT_ATTN_SPEC needs BERT_ATTN_MMASUM"
+#endif
 #ifndef BERT_ATTN_LDW
 #define BERT_ATTN_LDW 0
 #endif
@@ -278,6 +285,67 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                 mbar_wait(&s_full[gb & 1], (gb >> 1) & 1);
                 tc_fence_after_sync();
                 const uint32_t s_addr = lane_base + TM_S + (gb & 1) * 64;
+#if BERT_ATTN_SPEC
+                // Speculative form: the exponentials are taken against the CURRENT reference max while the row max of
+                // the block is formed alongside (no dependency between the two, so the FMNMX chain and the vote leave
+                // the per-block critical path); only if some row exceeds its reference by more than 2^8 -- rare after
+                // the first block -- the accumulator is rescaled and the block redone from the S tile still in TMEM.
+                const int kvalid = len - b * AK;
+                auto load_s = [&](float (&sv)[64]) {
+                    uint32_t r0[32], r1[32];
+                    tmem_ld_32x32b_x32(s_addr, r0);
+                    tmem_ld_32x32b_x32(s_addr + 32, r1);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) { sv[j] = __uint_as_float(r0[j]); sv[32 + j] = __uint_as_float(r1[j]); }
+                    if (kvalid < AK) {
+#pragma unroll
+                        for (int j = 0; j < 64; ++j) if (j >= kvalid) sv[j] = -INFINITY;
+                    }
+                };
+                auto row_max = [&](const float (&sv)[64]) {
+                    float mx4[4] = {sv[0], sv[1], sv[2], sv[3]};
+#pragma unroll
+                    for (int j = 4; j < 64; j += 4) {
+                        mx4[0] = fmaxf(mx4[0], sv[j]); mx4[1] = fmaxf(mx4[1], sv[j + 1]);
+                        mx4[2] = fmaxf(mx4[2], sv[j + 2]); mx4[3] = fmaxf(mx4[3], sv[j + 3]);
+                    }
+                    return fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * p.scale_log2;
+                };
+                auto exp_pack = [&](const float (&sv)[64], float mref, uint32_t (&pkv)[32]) {
+                    const float2 nm2 = make_float2(-mref, -mref), sc2 = make_float2(p.scale_log2, p.scale_log2);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const float2 x = __ffma2_rn(make_float2(sv[2 * j], sv[2 * j + 1]), sc2, nm2);
+                        const float2 e = (kPolyEvery > 0 && j % (kPolyEvery > 0 ? kPolyEvery : 1) == kPolyEvery - 1)
+                                             ? ex2_poly2(x) : make_float2(ex2f(x.x), ex2f(x.y));
+                        pkv[j] = pack_h2(e.x, e.y);
+                    }
+                };
+                float s[64];
+                uint32_t pk[32];
+                load_s(s);
+                const float mx = row_max(s);
+                if (b == 0) m_ref = mx;                         // first block: O is overwritten, nothing to rescale
+                exp_pack(s, m_ref, pk);
+                if (b >= 1 && __any_sync(0xffffffffu, mx > m_ref + kRescaleThreshold)) {
+                    float factor = 1.f;
+                    if (mx > m_ref + kRescaleThreshold) { factor = ex2f(m_ref - mx); m_ref = mx; }
+                    mbar_wait(&pv_done[(gb - 1) & 1], ((gb - 1) >> 1) & 1);
+                    tc_fence_after_sync();
+#pragma unroll 1
+                    for (int hh = 0; hh < 3; ++hh) {            // O (64 columns) and the row sums at TM_L = TM_O + 64
+                        uint32_t o[32];
+                        tmem_ld_32x32b_x32(lane_base + TM_O + hh * 32, o);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) o[j] = __float_as_uint(__uint_as_float(o[j]) * factor);
+                        tmem_st_32x32b_x32(lane_base + TM_O + hh * 32, o);
+                    }
+                    load_s(s);
+                    exp_pack(s, m_ref, pk);
+                }
+#else
                 uint32_t r0[32], r1[32];
 #if BERT_ATTN_LDW
                 tmem_ld_32x32b_x32x2_wait(s_addr, r0, s_addr + 32, r1);
@@ -335,6 +403,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                     pk[j] = pack_h2(e.x, e.y);
                 }
                 l += (sum[0].x + sum[0].y) + (sum[1].x + sum[1].y);
+#endif
                 tmem_st_32x32b_x32(s_addr, pk);               // P over the first half of this S buffer
                 tmem_st_wait();
                 tc_fence_before_sync();
