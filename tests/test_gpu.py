@@ -237,6 +237,10 @@ def test_full_size_properties_bge_base(pkg):
     perm = np.random.default_rng(0).permutation(64)
     e2 = m.encode([texts[i] for i in perm])
     assert np.abs(e2 - e[perm]).max() <= 4e-3
+    # run-to-run determinism at full size (many tiles per persistent CTA: a barrier / TMEM ordering bug shows up here
+    # long before it shows in the small kernel self-tests)
+    for _ in range(2):
+        assert np.array_equal(m.encode(texts), e)
     m.close()
 
 
