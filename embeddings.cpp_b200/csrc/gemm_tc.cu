@@ -27,6 +27,9 @@ constexpr int kSmemLimit = 232448;                   // 227 KB opt-in limit per 
 // EPB (fused LayerNorm, short K): the epilogue chain (residual load -> pass 1 -> statistics exchange -> pass 2 ->
 // stores) is longer than the mainloop of a tile, so smem goes to the epilogue instead of the rings: the q8 twin
 // gets its own staging buffer and the residual box of the NEXT tile is fetched while this tile is normalised.
+#ifndef BERT_EPI_LDX
+#define BERT_EPI_LDX 0
+#endif
 template <int BN, int WT, bool LN, bool RES, bool EPB = false> struct GemmCfg {
     static constexpr bool kQ4      = WT != W_F16;
     static constexpr int kBHalf    = BN / 2;                 // B rows this CTA supplies
@@ -587,15 +590,27 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     }
                     if (has_bias) bnext = __ldg(reinterpret_cast<const float2 *>(p.bias + c1) + lane);
                 }
+#if BERT_EPI_LDX
+                // diagnostic builds for the open item in profiles/r1_head.md: 1 = both halves up front, a wait after EACH load
+                uint32_t r2[2][32];
+                tmem_ld_32x32b_x32(tmem_base + ((uint32_t) (q * 32) << 16) + acc * Cfg::kAccStride + b * 64, r2[0]);
+                tmem_ld_wait();
+                tmem_ld_32x32b_x32(tmem_base + ((uint32_t) (q * 32) << 16) + acc * Cfg::kAccStride + b * 64 + 32, r2[1]);
+                tmem_ld_wait();
+#endif
 #pragma unroll
                 for (int hh = 0; hh < 2; ++hh) {
                     // one 32-column load in flight at a time: loading both halves of the box up front (two loads + one
                     // tcgen05.wait::ld, also as a single asm statement) measured 1 % faster but gave NON-DETERMINISTIC
                     // results at full size (tests/test_gpu.py::test_full_size_properties_bge_base failed 7 of 7 runs,
                     // this form 0 of 7; kernel self-tests pass either way).  Root cause open: profiles/r1_head.md
+#if BERT_EPI_LDX
+                    const uint32_t * r = r2[hh];
+#else
                     uint32_t r[32];
                     tmem_ld_32x32b_x32(tmem_base + ((uint32_t) (q * 32) << 16) + acc * Cfg::kAccStride + b * 64 + hh * 32, r);
                     tmem_ld_wait();
+#endif
                     float2 v[16];
 #pragma unroll
                     for (int i = 0; i < 16; ++i) v[i] = make_float2(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1]));
