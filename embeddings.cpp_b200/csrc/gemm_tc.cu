@@ -27,8 +27,18 @@ constexpr int kSmemLimit = 232448;                   // 227 KB opt-in limit per 
 // EPB (fused LayerNorm, short K): the epilogue chain (residual load -> pass 1 -> statistics exchange -> pass 2 ->
 // stores) is longer than the mainloop of a tile, so smem goes to the epilogue instead of the rings: the q8 twin
 // gets its own staging buffer and the residual box of the NEXT tile is fetched while this tile is normalised.
+#ifndef BERT_DQ_LDS_SINK
+#define BERT_DQ_LDS_SINK 0
+#endif
 #ifndef BERT_EPI_LDX
 #define BERT_EPI_LDX 0
+#endif
+#if BERT_EPI_LDX == 2
+// diagnostic: [0] words whose early read (both halves up front) differs from the late re-read, [1] words compared
+__device__ unsigned long long g_epi_ld_diag[2];
+extern "C" __attribute__((visibility("default"))) int bertx_debug_epi_ld(unsigned long long * out2) {
+    return (int) cudaMemcpyFromSymbol(out2, g_epi_ld_diag, sizeof(g_epi_ld_diag));
+}
 #endif
 template <int BN, int WT, bool LN, bool RES, bool EPB = false> struct GemmCfg {
     static constexpr bool kQ4      = WT != W_F16;
@@ -604,8 +614,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     // tcgen05.wait::ld, also as a single asm statement) measured 1 % faster but gave NON-DETERMINISTIC
                     // results at full size (tests/test_gpu.py::test_full_size_properties_bge_base failed 7 of 7 runs,
                     // this form 0 of 7; kernel self-tests pass either way).  Root cause open: profiles/r1_head.md
-#if BERT_EPI_LDX
+#if BERT_EPI_LDX == 1
                     const uint32_t * r = r2[hh];
+#elif BERT_EPI_LDX == 2
+                    // compute from the LATE read (the shipped order); count where the early read disagrees with it
+                    uint32_t r[32];
+                    tmem_ld_32x32b_x32(tmem_base + ((uint32_t) (q * 32) << 16) + acc * Cfg::kAccStride + b * 64 + hh * 32, r);
+                    tmem_ld_wait();
+                    {
+                        unsigned bad = 0;
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) bad += (r[i] != r2[hh][i]) ? 1u : 0u;
+                        if (bad) atomicAdd(&g_epi_ld_diag[0], (unsigned long long) bad);
+                        if (lane == 0 && hh == 1) atomicAdd(&g_epi_ld_diag[1], 2048ull);
+                    }
 #else
                     uint32_t r[32];
                     tmem_ld_32x32b_x32(tmem_base + ((uint32_t) (q * 32) << 16) + acc * Cfg::kAccStride + b * 64 + hh * 32, r);
@@ -695,6 +717,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         m[u] = WT == W_Q4_1 ? *reinterpret_cast<const __half *>(slot + Cfg::kNibBytes + Cfg::kScaleBytes + unit * 2) : __half();
                     }
                 }
+#if BERT_DQ_LDS_SINK
+                {   // the shared loads above must have LANDED (not just issued) before the slot is handed back to the bulk copy
+                    uint32_t sink;
+                    asm volatile("mov.b32 %0, %1;" : "=r"(sink) : "r"(nib[UNITS - 1].w ^ (uint32_t) __half_as_ushort(d[UNITS - 1]) ^ (uint32_t) __half_as_ushort(m[UNITS - 1])));
+                }
+#endif
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&n_empty[sn]);            // slot may be refilled
                 // dequantise into registers first (one 32-weight unit at a time: the register budget of these warps is small):
