@@ -27,11 +27,17 @@ namespace {
 constexpr int AQ = 128;            // queries per item
 constexpr int AK = 64;             // keys per block
 constexpr int AD = 64;             // head size
-constexpr int KV_STAGES = 4;
+#ifndef BERT_ATTN_KV_STAGES
+#define BERT_ATTN_KV_STAGES 4
+#endif
+#ifndef BERT_ATTN_Q_STAGES
+#define BERT_ATTN_Q_STAGES 1
+#endif
+constexpr int KV_STAGES = BERT_ATTN_KV_STAGES;
 constexpr int ATT_TC_THREADS = 192;
 constexpr int kQBytes = AQ * AD * 2;          // 16 KB
 constexpr int kKVBytes = AK * AD * 2;         // 8 KB each for K and V
-constexpr int Q_STAGES = 1;
+constexpr int Q_STAGES = BERT_ATTN_Q_STAGES;
 constexpr int kOutStage = 4 * 4096;            // per softmax warp: [32 rows][128 B] staging for coalesced output rows
 constexpr int kOnesBytes = 16 * 128;            // 16 rows x 64 fp16 of 1.0: K-major B operand (N = 16) of the row-sum MMA
 constexpr int kAttSmem = Q_STAGES * kQBytes + KV_STAGES * 2 * kKVBytes + kOutStage + kOnesBytes + 1024 /*align*/ + 256 /*barriers*/;
