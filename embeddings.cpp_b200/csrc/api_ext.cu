@@ -140,11 +140,55 @@ bool compare_h(const __half * da, const __half * db, size_t n, float * max_err, 
     *max_err = me; *max_ref = mr;
     return true;
 }
+
+// random test weight W[N][K] in the GEMM-ready device form (q4: random raw blocks in the FILE layout, repacked by
+// the production upload kernel)
+struct TestWeight {
+    DevBuf wbuf, nib, qd, qm;
+    DevWeight w;
+    int build(int N, int K, int wtype, const float * d_bias, std::mt19937 & rng) {
+        std::normal_distribution<float> nd(0.f, 1.f);
+        w.N = N; w.K = K; w.type = wtype; w.bias = d_bias; w.bn = gemm_pick_bn(N);
+        const float wscale = 1.0f / sqrtf((float) K);
+        if (wtype == W_F16) {
+            std::vector<uint16_t> hw((size_t) N * K);
+            for (auto & v : hw) v = f2h_bits(wscale * nd(rng));
+            if (!wbuf.alloc(hw.size() * 2)) return -3;
+            cudaMemcpy(wbuf.p, hw.data(), hw.size() * 2, cudaMemcpyHostToDevice);
+            w.w16 = wbuf.as<__half>();
+            if (!make_tmap_f16_2d(&w.tmap, w.w16, N, K, w.bn / 2)) return -4;
+            return 0;
+        }
+        const int bs = wtype == W_Q4_0 ? 18 : 20;
+        const size_t nblk = (size_t) N * (K / 32);
+        std::vector<uint8_t> raw(nblk * bs);
+        for (size_t b = 0; b < nblk; ++b) {
+            uint8_t * p = raw.data() + b * bs;
+            const uint16_t d = f2h_bits(wscale * (0.05f + fabsf(nd(rng))) / 4.f);
+            memcpy(p, &d, 2);
+            int off = 2;
+            if (wtype == W_Q4_1) { const uint16_t m = f2h_bits(-2.f * wscale * fabsf(nd(rng))); memcpy(p + 2, &m, 2); off = 4; }
+            for (int j = 0; j < 16; ++j) p[off + j] = (uint8_t) (rng() & 0xFF);
+        }
+        if (!wbuf.alloc(raw.size()) || !nib.alloc(nblk * 16) || !qd.alloc(nblk * 2) || !qm.alloc(nblk * 2)) return -3;
+        cudaMemcpy(wbuf.p, raw.data(), raw.size(), cudaMemcpyHostToDevice);
+        if (launch_repack_q4(wbuf.as<uint8_t>(), wtype, N, K, 0, N, nib.as<uint4>(), qd.as<__half>(), qm.as<__half>(), 0) != cudaSuccess) return -5;
+        w.qnib = nib.as<uint4>(); w.qd = qd.as<__half>(); w.qm = wtype == W_Q4_1 ? qm.as<__half>() : nullptr;
+        memset(&w.tmap, 0, sizeof(w.tmap));
+        return 0;
+    }
+};
+
+// device-side N(0, scale^2) fp16 fill (hash of the element index + Box-Muller): large test operands without host RNG time
+__global__ void fill_normal_h_kernel(__half * p, size_t n, uint32_t seed, float scale) {
+    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+        uint64_t z = (uint64_t) i * 0x9E3779B97F4A7C15ull + ((uint64_t) seed << 32 | 0x632BE5ABu);
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull; z = (z ^ (z >> 27)) * 0x94D049BB133111EBull; z ^= z >> 31;
+        const float u1 = ((uint32_t) z + 1.0f) * (1.0f / 4294967808.0f), u2 = (float) (uint32_t) (z >> 32) * (1.0f / 4294967296.0f);
+        p[i] = __float2half_rn(scale * sqrtf(-2.0f * __logf(u1)) * __cosf(6.2831853f * u2));
+    }
+}
 }  // namespace
-
-extern "C" {
-
-}  // extern "C"
 
 // reps == 0: run the tcgen05 kernel and the SIMT kernel once and compare;
 // reps  > 0: time `reps` back-to-back launches of the tcgen05 kernel (CUDA events, after one warm-up)
@@ -162,42 +206,16 @@ static int32_t gemm_test_impl(int32_t M, int32_t N, int32_t K, int32_t wtype, in
     for (auto & v : hres) v = f2h_bits(nd(rng));
     std::vector<float> hbias(N);
     for (auto & v : hbias) v = 0.5f * nd(rng);
-    DevBuf a, res, bias, o1, o2, wbuf, nib, qd, qm;
+    DevBuf a, res, bias, o1, o2;
     if (!a.alloc(ha.size() * 2) || !res.alloc(hres.size() * 2) || !bias.alloc((size_t) N * 4) ||
         !o1.alloc((size_t) M * N * 2) || !o2.alloc((size_t) M * N * 2)) return -3;
     cudaMemcpy(a.p, ha.data(), ha.size() * 2, cudaMemcpyHostToDevice);
     cudaMemcpy(res.p, hres.data(), hres.size() * 2, cudaMemcpyHostToDevice);
     cudaMemcpy(bias.p, hbias.data(), (size_t) N * 4, cudaMemcpyHostToDevice);
     cudaMemset(o1.p, 0xFF, (size_t) M * N * 2);
-    DevWeight w;
-    w.N = N; w.K = K; w.type = wtype; w.bias = bias.as<float>(); w.bn = gemm_pick_bn(N);
-    const float wscale = 1.0f / sqrtf((float) K);
-    if (wtype == W_F16) {
-        std::vector<uint16_t> hw((size_t) N * K);
-        for (auto & v : hw) v = f2h_bits(wscale * nd(rng));
-        if (!wbuf.alloc(hw.size() * 2)) return -3;
-        cudaMemcpy(wbuf.p, hw.data(), hw.size() * 2, cudaMemcpyHostToDevice);
-        w.w16 = wbuf.as<__half>();
-        if (!make_tmap_f16_2d(&w.tmap, w.w16, N, K, w.bn / 2)) return -4;
-    } else {
-        // random raw blocks in the FILE layout, repacked by the production upload kernel
-        const int bs = wtype == W_Q4_0 ? 18 : 20;
-        const size_t nblk = (size_t) N * (K / 32);
-        std::vector<uint8_t> raw(nblk * bs);
-        for (size_t b = 0; b < nblk; ++b) {
-            uint8_t * p = raw.data() + b * bs;
-            const uint16_t d = f2h_bits(wscale * (0.05f + fabsf(nd(rng))) / 4.f);
-            memcpy(p, &d, 2);
-            int off = 2;
-            if (wtype == W_Q4_1) { const uint16_t m = f2h_bits(-2.f * wscale * fabsf(nd(rng))); memcpy(p + 2, &m, 2); off = 4; }
-            for (int j = 0; j < 16; ++j) p[off + j] = (uint8_t) (rng() & 0xFF);
-        }
-        if (!wbuf.alloc(raw.size()) || !nib.alloc(nblk * 16) || !qd.alloc(nblk * 2) || !qm.alloc(nblk * 2)) return -3;
-        cudaMemcpy(wbuf.p, raw.data(), raw.size(), cudaMemcpyHostToDevice);
-        if (launch_repack_q4(wbuf.as<uint8_t>(), wtype, N, K, 0, N, nib.as<uint4>(), qd.as<__half>(), qm.as<__half>(), 0) != cudaSuccess) return -5;
-        w.qnib = nib.as<uint4>(); w.qd = qd.as<__half>(); w.qm = wtype == W_Q4_1 ? qm.as<__half>() : nullptr;
-        memset(&w.tmap, 0, sizeof(w.tmap));
-    }
+    TestWeight tw_;
+    { const int rc = tw_.build(N, K, wtype, bias.as<float>(), rng); if (rc) return rc; }
+    DevWeight & w = tw_.w;
     CUtensorMap tma, tmo, tmr;
     if (!make_tmap_f16_2d(&tma, a.p, rows, K, 128)) return -4;
     if (!make_tmap_f16_2d(&tmr, res.p, M, N, 32)) return -4;
@@ -349,6 +367,54 @@ int32_t bertx_bench_attention(int32_t n_sent, int32_t len, int32_t n_head, int32
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     *ms_total = ms;
     return ok ? 0 : -6;
+}
+
+// Debug (profiles/r2_gemm_race.md): one GEMM at ANY size -- device-generated A (and residual), the tcgen05 kernel run `runs`
+// times, the SIMT validation kernel once; all outputs are copied to the caller's host arrays ([M][N] fp16 bit patterns)
+// for element-wise analysis (tools/gemm_race.py).  The residual is only generated when the epilogue asks for it.
+int32_t bertx_debug_gemm(int32_t M, int32_t N, int32_t K, int32_t wtype, int32_t epilogue, int32_t seed, int32_t runs,
+                         uint16_t * out_ref, uint16_t * out_tc, float * ms_tc) {
+    if (M <= 0 || N % 64 || K % 64 || wtype < 1 || wtype > 3 || runs <= 0 || (epilogue & EPI_LN)) return -1;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { fprintf(stderr, "bertx_debug_gemm: no CUDA device\n"); return -2; }
+    cudaDeviceProp prop; cudaGetDeviceProperties(&prop, 0);
+    std::mt19937 rng((uint32_t) seed);
+    std::normal_distribution<float> nd(0.f, 1.f);
+    const size_t rows = ((size_t) M + 127) / 128 * 128;
+    const size_t n_out = (size_t) M * N;
+    DevBuf a, res, bias, o1, o2;
+    if (!a.alloc(rows * K * 2) || !bias.alloc((size_t) N * 4) || !o1.alloc(n_out * 2) || !o2.alloc(n_out * 2)) return -3;
+    if ((epilogue & EPI_RESIDUAL) && !res.alloc(n_out * 2)) return -3;
+    cudaMemset(a.p, 0, rows * K * 2);
+    fill_normal_h_kernel<<<2048, 256>>>(a.as<__half>(), (size_t) M * K, (uint32_t) seed, 1.0f);
+    if (res.p) fill_normal_h_kernel<<<2048, 256>>>(res.as<__half>(), n_out, (uint32_t) seed + 77u, 1.0f);
+    std::vector<float> hbias(N);
+    for (auto & v : hbias) v = 0.5f * nd(rng);
+    cudaMemcpy(bias.p, hbias.data(), (size_t) N * 4, cudaMemcpyHostToDevice);
+    TestWeight tw;
+    { const int rc = tw.build(N, K, wtype, bias.as<float>(), rng); if (rc) return rc; }
+    CUtensorMap tma, tmo, tmr;
+    if (!make_tmap_f16_2d(&tma, a.p, rows, K, 128)) return -4;
+    if (!make_tmap_f16_2d(&tmo, o1.p, M, N, 32)) return -4;
+    if (res.p && !make_tmap_f16_2d(&tmr, res.p, M, N, 32)) return -4;
+    const int fq = wtype == W_Q4_1 ? W_Q4_1 : W_Q4_0;
+    GemmArgs g1{&tma, &tmo, res.p ? &tmr : nullptr, a.as<__half>(), &tw.w, res.as<__half>(), o1.as<__half>(), M, epilogue, fq};
+    GemmArgs g2 = g1; g2.out = o2.as<__half>();
+    if (!cuda_ok(launch_gemm_simt(g2, 0), "debug gemm_simt launch") || !cuda_ok(cudaDeviceSynchronize(), "debug gemm_simt")) return -7;
+    if (cudaMemcpy(out_ref, o2.p, n_out * 2, cudaMemcpyDeviceToHost) != cudaSuccess) return -8;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    for (int r = 0; r < runs; ++r) {
+        cudaMemset(o1.p, 0xFF, n_out * 2);
+        cudaEventRecord(e0, 0);
+        if (!cuda_ok(launch_gemm_tc(g1, prop.multiProcessorCount, 0), "debug gemm_tc launch")) return -6;
+        cudaEventRecord(e1, 0);
+        if (!cuda_ok(cudaDeviceSynchronize(), "debug gemm_tc")) return -6;
+        if (ms_tc) cudaEventElapsedTime(&ms_tc[r], e0, e1);
+        if (cudaMemcpy(out_tc + (size_t) r * n_out, o1.p, n_out * 2, cudaMemcpyDeviceToHost) != cudaSuccess) return -8;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return 0;
 }
 
 }  // extern "C"

@@ -33,6 +33,16 @@ constexpr int kSmemLimit = 232448;                   // 227 KB opt-in limit per 
 #ifndef BERT_EPI_LDX
 #define BERT_EPI_LDX 0
 #endif
+// diagnostic knobs for the epilogue item of profiles/r2_gemm_race.md (defaults = the shipped kernel)
+#ifndef BERT_XCTA_RELEASE
+#define BERT_XCTA_RELEASE 0      // 1: cross-CTA arrives (b_full, tempty) release at cluster scope, MMA-side waits acquire at cluster scope
+#endif
+#ifndef BERT_EPI_STORE_WAIT_ALL
+#define BERT_EPI_STORE_WAIT_ALL 0  // 1: the staging buffer is only reused after the previous TMA store completed its global writes
+#endif
+#ifndef BERT_EPI_DELAY_NS
+#define BERT_EPI_DELAY_NS 0        // > 0: every epilogue warp sleeps this long before it hands the accumulator back
+#endif
 #if BERT_EPI_LDX == 2
 // diagnostic: [0] words whose early read (both halves up front) differs from the late re-read, [1] words compared
 __device__ unsigned long long g_epi_ld_diag[2];
@@ -64,8 +74,16 @@ template <int BN, int WT, bool LN, bool RES, bool EPB = false> struct GemmCfg {
     // fp16 weights: A and B travel together through one ring.  q4 weights: A needs TMA-latency depth,
     // the dequantised B only a short ring (it is produced from smem), the 4-bit ring hides L2 latency.
     static constexpr int kFitF16   = (kSmemLimit - kFixed) / (kABytes + kBBytes);
+#ifdef BERT_GEMM_SA
+    static constexpr int kSA       = kQ4 ? (LN ? (EPB ? 3 : 4) : BERT_GEMM_SA) : (kFitF16 > 6 ? 6 : kFitF16);
+#else
     static constexpr int kSA       = kQ4 ? (LN ? (EPB ? 3 : 4) : 5) : (kFitF16 > 6 ? 6 : kFitF16);
+#endif
+#ifdef BERT_GEMM_SB
+    static constexpr int kSB       = kQ4 ? (RES ? (EPB ? 2 : 3) : BERT_GEMM_SB) : kSA;
+#else
     static constexpr int kSB       = kQ4 ? (RES ? (EPB ? 2 : 3) : (BN > 192 ? 5 : 6)) : kSA;
+#endif
     // (the 4-bit ring depth stays a multiple of the number of dequant groups, so a slot is always
     // refilled for the same group that drained it)
     static constexpr int kSN       = kQ4 ? 6 : 0;
@@ -293,12 +311,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             for (int it = 0; it < my_tiles; ++it) {
                 const int acc = it & 1;
                 const uint32_t acc_ph = (it >> 1) & 1;
+#if BERT_XCTA_RELEASE
+                mbar_wait_cluster_acquire(&tempty[acc], acc_ph ^ 1);
+#else
                 mbar_wait(&tempty[acc], acc_ph ^ 1);
+#endif
                 tc_fence_after_sync();
                 const uint32_t d_tmem = tmem_base + acc * Cfg::kAccStride;
                 for (int kb = 0; kb < num_k; ++kb) {
                     mbar_wait(&a_full[sa], pha);
+#if BERT_XCTA_RELEASE
+                    if (Q4) mbar_wait_cluster_acquire(&b_full[sb], phb);
+#else
                     if (Q4) mbar_wait(&b_full[sb], phb);
+#endif
                     tc_fence_after_sync();
                     if (elect_one()) {
                         const uint64_t adesc = umma_smem_desc_sw128(smem_u32(smem_a + sa * Cfg::kABytes));
@@ -662,7 +688,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     if (p.epilogue & EPI_FAKEQUANT) fake_quant32_v2(v, p.fq_type);
                     if (hh == 0) {
                         // the TMA store of this warp's previous box must be done reading the staging buffer
+#if BERT_EPI_STORE_WAIT_ALL
+                        if (lane == 0) tma_store_wait_all<0>();
+#else
                         if (lane == 0) tma_store_wait_read<0>();
+#endif
                         __syncwarp();
                     }
 #pragma unroll
@@ -684,7 +714,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             }
             tc_fence_before_sync();
             __syncwarp();
+#if BERT_EPI_DELAY_NS > 0
+            __nanosleep(BERT_EPI_DELAY_NS);
+#endif
+#if BERT_XCTA_RELEASE
+            if (lane == 0) mbar_arrive_cluster_release(tempty_leader + 8 * acc);
+#else
             if (lane == 0) mbar_arrive_cluster(tempty_leader + 8 * acc);
+#endif
         }
         if (lane == 0) tma_store_wait_all<0>();
       }
@@ -760,7 +797,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 }
                 fence_proxy_async_smem();
                 __syncwarp();
+#if BERT_XCTA_RELEASE
+                if (lane == 0) mbar_arrive_cluster_release(bfull_leader + 8 * sb);
+#else
                 if (lane == 0) mbar_arrive_cluster(bfull_leader + 8 * sb);
+#endif
                 sn += DQ_GROUPS; if (sn >= SN) { sn -= SN; phn ^= 1; }
                 sb += DQ_GROUPS; if (sb >= SB) { sb -= SB; phb ^= 1; }
             }
@@ -811,7 +852,10 @@ static cudaError_t launch_one(const GemmArgs & g, int num_sms, cudaStream_t st) 
     const int num_m = (g.M + 2 * BM - 1) / (2 * BM), num_n = w.N / BN;
     const int csize = LN ? 2 * num_n : 2;                 // CTAs per cluster
     const int units = LN ? num_m : num_m * num_n;         // stripes or tiles to hand out
-    const int ncl_max = max_clusters<BN, WT, LN, RES, EPB>(device, num_sms, csize);
+    int ncl_max = max_clusters<BN, WT, LN, RES, EPB>(device, num_sms, csize);
+    // BERT_GEMM_MAX_CLUSTERS (debug): fewer persistent clusters -> many tiles per cluster at small M (sanitizer runs)
+    static const int ncl_cap = [] { const char * e = getenv("BERT_GEMM_MAX_CLUSTERS"); return e ? atoi(e) : 0; }();
+    if (ncl_cap > 0 && ncl_max > ncl_cap) ncl_max = ncl_cap;
     const int ncl = units < ncl_max ? units : ncl_max;
     if (ncl <= 0) return cudaSuccess;
     if ((g.epilogue & EPI_RESIDUAL) && !g.tmap_res) return cudaErrorInvalidValue;

@@ -77,6 +77,12 @@ BERT_API int32_t bertx_selftest_attention(int32_t n_sent, int32_t max_len, int32
 BERT_API int32_t bertx_bench_attention(int32_t n_sent, int32_t len, int32_t n_head, int32_t d_head, int32_t reps,
                                        float * ms_total);
 
+/* Debug aid for kernel bisects: one GEMM of ANY size on device-generated operands; the SIMT validation kernel's output
+ * and `runs` outputs of the tcgen05 kernel ([M][N] fp16 bit patterns each) are copied to host arrays the caller owns,
+ * ms_tc[runs] receives the kernel times.  Fused-LayerNorm epilogues are not supported here. */
+BERT_API int32_t bertx_debug_gemm(int32_t M, int32_t N, int32_t K, int32_t wtype, int32_t epilogue, int32_t seed,
+                                  int32_t runs, uint16_t * out_ref, uint16_t * out_tc, float * ms_tc);
+
 /* Model quantiser: fname_inp (f32 / f16 file) -> fname_out with every 2-D "*weight" tensor as
  * q4_0 (itype 2) or q4_1 (itype 3) blocks, byte-identical to the reference's `quantize` tool
  * (models/quantize.cpp:27-268, `./quantize in.bin out.bin type`; block arithmetic ggml.c:942-1018).  The block
