@@ -28,6 +28,15 @@ def build(force=False):
     return mod.build(force=force)
 
 
+def build_perturbed(force=False):
+    """The timing-perturbed builds of the GEMM kernel (build.py PERTURBED) -> list of library paths."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("_b200_build", os.path.join(HERE, "build.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod.build_perturbed(force=force)
+
+
 def lib():
     """The loaded C-ABI library with argtypes set (raises if it has not been built)."""
     global _lib

@@ -20,7 +20,7 @@ FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std
          "-Xcompiler", "-fPIC,-fvisibility=hidden,-pthread", "-I", os.path.join(HERE, "..", "include")]
 if os.environ.get("BERT_DEBUG_WAIT"):
     FLAGS.append("-DBERT_DEBUG_WAIT")
-SOURCES = ["gemm_tc.cu", "attention.cu", "attention_tc.cu", "rowwise.cu", "upload.cu", "engine_load.cu", "engine_run.cu",
+SOURCES = ["gemm_tc.cu", "attention.cu", "attention_tc.cu", "rowwise.cu", "upload.cu", "engine_load.cu", "engine_run.cu", "pipeline.cu",
            "api.cu", "api_ext.cu", "quantize.cu", "tokenizer.cpp", "model_file.cpp"]
 
 
@@ -61,6 +61,42 @@ def build(force=False, verbose=True):
     if jobs or not os.path.exists(lib):
         run([NVCC, "-shared", "-cudart", "static", "-o", lib] + objs + ["-lpthread", "-ldl", "-lrt"])
     return lib
+
+
+# Timing perturbations of the GEMM kernel for tests/test_gpu.py::test_full_size_determinism_under_perturbed_builds (the round-2
+# mainloop race only showed under such shifts, profiles/r2_gemm_race.md): name -> extra flags for gemm_tc.cu
+PERTURBED = {
+    "ldx0": ["-DBERT_EPI_LDX=0"],                        # one epilogue TMEM load in flight at a time
+    "dq1": ["-DBERT_DQ_SYNC=1"],                         # every dequant thread arrives on b_full itself
+    "sa4sb4": ["-DBERT_GEMM_SA=4", "-DBERT_GEMM_SB=4"],  # A and B rings one stage shorter
+}
+
+
+def build_variant(name, src, flags, force=False):
+    """libbert.so with ONE source recompiled with extra flags -> lib/variants/libbert_<name>.so (pick it with BERT_B200_LIB)."""
+    build(verbose=False)
+    stem = src.rsplit(".", 1)[0]
+    vobj, vlib = os.path.join(OBJ, "variants"), os.path.join(LIB, "variants")
+    os.makedirs(vobj, exist_ok=True)
+    os.makedirs(vlib, exist_ok=True)
+    obj = os.path.join(vobj, f"{name}_{stem}.o")
+    lib = os.path.join(vlib, f"libbert_{name}.so")
+    default_lib = os.path.join(LIB, "libbert.so")
+    if not force and os.path.exists(lib) and os.path.getmtime(lib) >= os.path.getmtime(default_lib):
+        return lib
+    r = subprocess.run([NVCC] + FLAGS + list(flags) + ["-c", os.path.join(SRC, src), "-o", obj], capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("nvcc failed for variant " + name + "\n" + r.stdout + r.stderr)
+    objs = [obj if s.rsplit(".", 1)[0] == stem else os.path.join(OBJ, s.rsplit(".", 1)[0] + ".o") for s in SOURCES]
+    r = subprocess.run([NVCC, "-shared", "-cudart", "static", "-o", lib] + objs + ["-lpthread", "-ldl", "-lrt"], capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("link failed for variant " + name + "\n" + r.stdout + r.stderr)
+    return lib
+
+
+def build_perturbed(force=False):
+    with ThreadPoolExecutor(max_workers=len(PERTURBED)) as ex:
+        return list(ex.map(lambda kv: build_variant(kv[0], "gemm_tc.cu", kv[1], force), PERTURBED.items()))
 
 
 if __name__ == "__main__":

@@ -62,117 +62,6 @@ bool tokenize_all(Engine & e, int n_threads, int n, const char ** texts, std::ve
 }
 
 
-// bert_encode_batch as a two-stage pipeline (replaces the reference's "tokenise everything into an
-// n_inputs x n_max_tokens scratch, then run" -- bert.cpp:1395-1405 -- which is 1 GB of scratch per 512 K inputs
-// and leaves the accelerator idle while the host tokenises).  Worker threads tokenise blocks of kBlock
-// sentences in input order; the calling thread takes finished blocks in order, and as soon as it holds one
-// chunk (>= one token-budget micro-batch per GPU, twice that with several GPUs so each GPU's staging ring
-// stays full) it runs it on the GPUs while the workers carry on with the following blocks.  Workers run at
-// most ~4 chunks of tokens ahead, so host memory is bounded whatever n_inputs is.
-struct TokBlock {
-    std::vector<int32_t> ids, lens;
-    bool ready = false;
-};
-
-bool encode_pipelined(Engine & e, int n_threads, int n, const char ** texts, float ** out) {
-    const int N = e.hp.n_max_tokens;
-    constexpr int kBlock = 8;
-    if (n <= 2 * kBlock) {                                    // latency path: no threads
-        std::vector<int32_t> ids((size_t) n * N), lens(n);
-        std::vector<const int32_t *> ptrs(n);
-        for (int i = 0; i < n; ++i) {
-            ptrs[i] = ids.data() + (size_t) i * N;
-            lens[i] = e.tok.tokenize(texts[i], ids.data() + (size_t) i * N, N);
-        }
-        return e.run_tokens(ptrs.data(), lens.data(), n, out);
-    }
-    const int nblocks = (n + kBlock - 1) / kBlock;
-    int nt = n_threads > 0 ? n_threads : 1;
-    const int hw = (int) std::thread::hardware_concurrency();
-    if (hw > 0 && nt > hw) nt = hw;
-    if (nt > nblocks) nt = nblocks;
-    const size_t nd = e.reps.size() > 0 ? e.reps.size() : 1;
-    const int64_t target = (int64_t) e.t_cap * (int64_t) nd * (nd > 1 ? 2 : 1);
-    const int64_t window = 4 * target;
-
-    std::vector<TokBlock> blocks(nblocks);
-    std::mutex m;
-    std::condition_variable cv_ready, cv_space;
-    int next_block = 0, consumer_pos = 0;                    // guarded by m
-    int64_t produced = 0, consumed = 0;                      // tokens, guarded by m
-    bool abort = false;
-
-    auto worker = [&]() {
-        std::vector<int32_t> scratch((size_t) kBlock * N);
-        int32_t lens[kBlock];
-        while (true) {
-            int b;
-            {
-                std::unique_lock<std::mutex> g(m);
-                b = next_block++;
-                if (b >= nblocks) return;
-                // the blocks the consumer is waiting for always go ahead; later ones respect the window
-                cv_space.wait(g, [&] { return abort || b < consumer_pos + nt || produced - consumed <= window; });
-                if (abort) return;
-            }
-            const int lo = b * kBlock, hi = lo + kBlock < n ? lo + kBlock : n;
-            size_t off = 0;
-            for (int i = lo; i < hi; ++i) {
-                lens[i - lo] = e.tok.tokenize(texts[i], scratch.data() + off, N);
-                off += (size_t) lens[i - lo];
-            }
-            TokBlock & tb = blocks[b];
-            tb.ids.assign(scratch.begin(), scratch.begin() + off);
-            tb.lens.assign(lens, lens + (hi - lo));
-            {
-                std::lock_guard<std::mutex> g(m);
-                tb.ready = true;
-                produced += (int64_t) off;
-            }
-            cv_ready.notify_one();
-        }
-    };
-    std::vector<std::thread> th;
-    th.reserve(nt);
-    for (int t = 0; t < nt; ++t) th.emplace_back(worker);
-
-    bool ok = true;
-    std::vector<const int32_t *> ptrs;
-    std::vector<int32_t> lens;
-    int pos = 0;
-    while (pos < nblocks && ok) {
-        const int first_block = pos;
-        int64_t chunk_tokens = 0;
-        while (pos < nblocks) {
-            {
-                std::unique_lock<std::mutex> g(m);
-                cv_ready.wait(g, [&] { return blocks[pos].ready; });
-                consumer_pos = pos + 1;
-            }
-            cv_space.notify_all();
-            chunk_tokens += (int64_t) blocks[pos].ids.size();
-            ++pos;
-            if (chunk_tokens >= target) break;
-        }
-        ptrs.clear(); lens.clear();
-        for (int b = first_block; b < pos; ++b) {
-            const TokBlock & tb = blocks[b];
-            size_t off = 0;
-            for (int32_t l : tb.lens) { ptrs.push_back(tb.ids.data() + off); lens.push_back(l); off += (size_t) l; }
-        }
-        ok = e.run_tokens(ptrs.data(), lens.data(), (int) ptrs.size(), out + (size_t) first_block * kBlock);
-        for (int b = first_block; b < pos; ++b) { std::vector<int32_t>().swap(blocks[b].ids); std::vector<int32_t>().swap(blocks[b].lens); }
-        {
-            std::lock_guard<std::mutex> g(m);
-            consumed += chunk_tokens;
-            if (!ok) abort = true;
-        }
-        cv_space.notify_all();
-    }
-    for (auto & t : th) t.join();
-    return ok;
-}
-
 }  // namespace
 
 extern "C" {
@@ -233,6 +122,7 @@ struct bert_ctx * bertx_load_host_only(const char * fname) {
         if (!mf.load(fname)) return nullptr;
         bert_ctx * ctx = new bert_ctx;
         ctx->eng.hp = mf.hp;
+        ctx->eng.init_limits();
         std::vector<std::string> vocab = mf.vocab;
         ctx->eng.tok.build(std::move(vocab));
         fflush(stdout);
@@ -284,7 +174,7 @@ void bert_encode_batch(struct bert_ctx * ctx, int32_t n_threads, int32_t n_batch
     if (n_inputs <= 0) return;
     try {
         std::lock_guard<std::mutex> lock(ctx->eng.mu);
-        if (!encode_pipelined(ctx->eng, n_threads, n_inputs, texts, embeddings)) {
+        if (!ctx->eng.encode_texts(n_threads, n_inputs, texts, embeddings)) {
             fprintf(stderr, "%s: failed, outputs of unfinished inputs left untouched\n", __func__);
         }
     } catch (const std::exception & ex) {
@@ -308,6 +198,20 @@ int32_t bertx_hparam(struct bert_ctx * ctx, int32_t index) {
 }
 
 int64_t bertx_kernel_launches(struct bert_ctx * ctx) { return ctx->eng.launches.load(); }
+
+int32_t bertx_plan(struct bert_ctx * ctx, int32_t n_devices, int32_t n_sent, const int32_t * n_tokens,
+                   int32_t * mb_of_sentence, int32_t * mb_tokens, int32_t cap) {
+    try {
+        if (!ctx || n_sent <= 0 || n_devices <= 0) return -1;
+        std::vector<int> mbt;
+        const int n = ctx->eng.plan_encode(n_tokens, n_sent, n_devices, mb_of_sentence, mbt);
+        if (n > cap) return -2;
+        for (int i = 0; i < n; ++i) mb_tokens[i] = mbt[i];
+        return n;
+    } catch (...) {
+        return -3;
+    }
+}
 
 int32_t bertx_set_pooling(struct bert_ctx * ctx, int32_t mode) {
     if (!ctx || (mode != 0 && mode != 1)) return -1;

@@ -370,11 +370,13 @@ int32_t bertx_bench_attention(int32_t n_sent, int32_t len, int32_t n_head, int32
 }
 
 // Debug (profiles/r2_gemm_race.md): one GEMM at ANY size -- device-generated A (and residual), the tcgen05 kernel run `runs`
-// times, the SIMT validation kernel once; all outputs are copied to the caller's host arrays ([M][N] fp16 bit patterns)
-// for element-wise analysis (tools/gemm_race.py).  The residual is only generated when the epilogue asks for it.
+// times, the SIMT validation kernel (+ the stand-alone LayerNorm kernel for EPI_LN) once; all outputs are copied to the
+// caller's host arrays ([M][N] fp16 bit patterns) for element-wise analysis (tools/gemm_race.py).  out_ref == NULL skips the
+// validation kernel; out_ref2 / out_tc2 receive the q8 twin of a fused-LayerNorm epilogue (NULL: not wanted).
 int32_t bertx_debug_gemm(int32_t M, int32_t N, int32_t K, int32_t wtype, int32_t epilogue, int32_t seed, int32_t runs,
-                         uint16_t * out_ref, uint16_t * out_tc, float * ms_tc) {
-    if (M <= 0 || N % 64 || K % 64 || wtype < 1 || wtype > 3 || runs <= 0 || (epilogue & EPI_LN)) return -1;
+                         uint16_t * out_ref, uint16_t * out_tc, float * ms_tc, uint16_t * out_ref2, uint16_t * out_tc2,
+                         uint16_t * a_out, float * w_out) {
+    if (M <= 0 || N % 64 || K % 64 || wtype < 1 || wtype > 3 || runs <= 0 || !out_tc) return -1;
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { fprintf(stderr, "bertx_debug_gemm: no CUDA device\n"); return -2; }
     cudaDeviceProp prop; cudaGetDeviceProperties(&prop, 0);
@@ -382,7 +384,8 @@ int32_t bertx_debug_gemm(int32_t M, int32_t N, int32_t K, int32_t wtype, int32_t
     std::normal_distribution<float> nd(0.f, 1.f);
     const size_t rows = ((size_t) M + 127) / 128 * 128;
     const size_t n_out = (size_t) M * N;
-    DevBuf a, res, bias, o1, o2;
+    const bool ln = (epilogue & EPI_LN) != 0, twin = ln && (epilogue & EPI_FAKEQUANT);
+    DevBuf a, res, bias, o1, o2, o1q, o2q, y2, lng, lnb;
     if (!a.alloc(rows * K * 2) || !bias.alloc((size_t) N * 4) || !o1.alloc(n_out * 2) || !o2.alloc(n_out * 2)) return -3;
     if ((epilogue & EPI_RESIDUAL) && !res.alloc(n_out * 2)) return -3;
     cudaMemset(a.p, 0, rows * K * 2);
@@ -393,25 +396,61 @@ int32_t bertx_debug_gemm(int32_t M, int32_t N, int32_t K, int32_t wtype, int32_t
     cudaMemcpy(bias.p, hbias.data(), (size_t) N * 4, cudaMemcpyHostToDevice);
     TestWeight tw;
     { const int rc = tw.build(N, K, wtype, bias.as<float>(), rng); if (rc) return rc; }
-    CUtensorMap tma, tmo, tmr;
+    CUtensorMap tma, tmo, tmr, tmo2;
     if (!make_tmap_f16_2d(&tma, a.p, rows, K, 128)) return -4;
     if (!make_tmap_f16_2d(&tmo, o1.p, M, N, 32)) return -4;
     if (res.p && !make_tmap_f16_2d(&tmr, res.p, M, N, 32)) return -4;
     const int fq = wtype == W_Q4_1 ? W_Q4_1 : W_Q4_0;
     GemmArgs g1{&tma, &tmo, res.p ? &tmr : nullptr, a.as<__half>(), &tw.w, res.as<__half>(), o1.as<__half>(), M, epilogue, fq};
-    GemmArgs g2 = g1; g2.out = o2.as<__half>();
-    if (!cuda_ok(launch_gemm_simt(g2, 0), "debug gemm_simt launch") || !cuda_ok(cudaDeviceSynchronize(), "debug gemm_simt")) return -7;
-    if (cudaMemcpy(out_ref, o2.p, n_out * 2, cudaMemcpyDeviceToHost) != cudaSuccess) return -8;
+    if (ln) {
+        std::vector<float> hg(N), hb(N);
+        for (auto & v : hg) v = 1.0f + 0.2f * nd(rng);
+        for (auto & v : hb) v = 0.3f * nd(rng);
+        if (!o1q.alloc(n_out * 2) || !o2q.alloc(n_out * 2) || !y2.alloc(n_out * 2) || !lng.alloc((size_t) N * 4) || !lnb.alloc((size_t) N * 4)) return -3;
+        cudaMemcpy(lng.p, hg.data(), (size_t) N * 4, cudaMemcpyHostToDevice);
+        cudaMemcpy(lnb.p, hb.data(), (size_t) N * 4, cudaMemcpyHostToDevice);
+        if (!make_tmap_f16_2d(&tmo2, o1q.p, M, N, 32)) return -4;
+        g1.tmap_out2 = &tmo2; g1.ln_gamma = lng.as<float>(); g1.ln_beta = lnb.as<float>();
+    }
+    if (a_out && cudaMemcpy(a_out, a.p, (size_t) M * K * 2, cudaMemcpyDeviceToHost) != cudaSuccess) return -8;
+    if (w_out) {                                     // the weights as the kernels decode them, f32 [N][K]
+        DevBuf wf;
+        if (!wf.alloc((size_t) N * K * 4)) return -3;
+        if (wtype == W_F16) {
+            std::vector<__half> hw((size_t) N * K);
+            cudaMemcpy(hw.data(), tw.w.w16, hw.size() * 2, cudaMemcpyDeviceToHost);
+            for (size_t i = 0; i < hw.size(); ++i) w_out[i] = __half2float(hw[i]);
+        } else {
+            if (!cuda_ok(launch_dequant_q4_f32(tw.w, wf.as<float>(), 0), "debug dequant") || !cuda_ok(cudaDeviceSynchronize(), "debug dequant")) return -7;
+            if (cudaMemcpy(w_out, wf.p, (size_t) N * K * 4, cudaMemcpyDeviceToHost) != cudaSuccess) return -8;
+        }
+    }
+    if (out_ref) {
+        GemmArgs g2 = g1;
+        if (ln) {
+            g2.out = y2.as<__half>(); g2.epilogue = EPI_BIAS | EPI_RESIDUAL;
+            if (!cuda_ok(launch_gemm_simt(g2, 0), "debug gemm_simt launch")) return -7;
+            if (!cuda_ok(launch_ln(y2.as<__half>(), lng.as<float>(), lnb.as<float>(), M, N, o2.as<__half>(), twin ? o2q.as<__half>() : nullptr, fq, 0), "debug ln launch")) return -7;
+        } else {
+            g2.out = o2.as<__half>();
+            if (!cuda_ok(launch_gemm_simt(g2, 0), "debug gemm_simt launch")) return -7;
+        }
+        if (!cuda_ok(cudaDeviceSynchronize(), "debug gemm_simt")) return -7;
+        if (cudaMemcpy(out_ref, o2.p, n_out * 2, cudaMemcpyDeviceToHost) != cudaSuccess) return -8;
+        if (twin && out_ref2 && cudaMemcpy(out_ref2, o2q.p, n_out * 2, cudaMemcpyDeviceToHost) != cudaSuccess) return -8;
+    }
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
     for (int r = 0; r < runs; ++r) {
         cudaMemset(o1.p, 0xFF, n_out * 2);
+        if (twin) cudaMemset(o1q.p, 0xFF, n_out * 2);
         cudaEventRecord(e0, 0);
         if (!cuda_ok(launch_gemm_tc(g1, prop.multiProcessorCount, 0), "debug gemm_tc launch")) return -6;
         cudaEventRecord(e1, 0);
         if (!cuda_ok(cudaDeviceSynchronize(), "debug gemm_tc")) return -6;
         if (ms_tc) cudaEventElapsedTime(&ms_tc[r], e0, e1);
         if (cudaMemcpy(out_tc + (size_t) r * n_out, o1.p, n_out * 2, cudaMemcpyDeviceToHost) != cudaSuccess) return -8;
+        if (twin && out_tc2 && cudaMemcpy(out_tc2 + (size_t) r * n_out, o1q.p, n_out * 2, cudaMemcpyDeviceToHost) != cudaSuccess) return -8;
     }
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     return 0;

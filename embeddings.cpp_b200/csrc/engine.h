@@ -4,8 +4,13 @@
 // (bert.cpp:827-1147, ggml.c:17164-17670) and its arena sizing (bert.cpp:788-810).
 #pragma once
 #include <atomic>
+#include <condition_variable>
+#include <deque>
+#include <functional>
+#include <memory>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "kernels.cuh"
@@ -26,12 +31,50 @@ struct MicroBatch {
     size_t tok_offset = 0;          // offset of its first id in the job's packed id array
 };
 
+// One bert_encode_batch / bert_forward_batch call in flight: the calling thread submits micro-batches and waits here.
+struct JobState {
+    std::mutex m;
+    std::condition_variable cv;
+    int pending = 0;                 // micro-batches submitted and not yet scattered to the caller
+    int64_t retired_tokens = 0;      // tokens of the micro-batches that are done (back-pressure for the tokenizer threads)
+    bool ok = true;
+};
+
+// A micro-batch ready to run on whichever GPU takes it: per-sentence token pointers, lengths and output rows in PACK order.
+struct MbTask {
+    std::shared_ptr<void> keep;      // owner of the token storage (null when the caller owns it)
+    std::vector<const int32_t *> tok;
+    std::vector<int32_t> len;
+    std::vector<float *> out;
+    int tokens = 0, max_len = 0;
+    JobState * job = nullptr;
+};
+
+// Persistent host threads for the tokenizer (no thread creation per call): run(n, fn) starts fn(0..n-1) on n pool threads
+// and returns at once; wait() blocks until all of them have returned.
+class HostPool {
+public:
+    ~HostPool();
+    void run(int n, std::function<void(int)> fn);
+    void wait();
+private:
+    void body(int idx, uint64_t seen);
+    std::vector<std::thread> th_;
+    std::mutex m_;
+    std::condition_variable cv_, done_cv_;
+    std::function<void(int)> fn_;
+    uint64_t gen_ = 0;
+    int want_ = 0, active_ = 0;
+    bool stop_ = false;
+};
+
 enum KernelKind { KK_EMBED = 0, KK_GEMM = 1, KK_ATTN = 2, KK_LN = 3, KK_POOL = 4, KK_OTHER = 5, KK_COUNT = 8 };
 
 struct Replica {
     int device = -1;
     int num_sms = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;                // compute
+    cudaStream_t copy_in = nullptr, copy_out = nullptr;   // H2D of the next micro-batch / D2H of the previous one overlap the forward
     std::vector<void *> allocs;      // every cudaMalloc of this replica
     std::vector<void *> pinned;
 
@@ -50,14 +93,16 @@ struct Replica {
     CUtensorMap ta_q, ta_kv;                         // attention maps over qkv (box 64 x 128 / 64 x 64)
     CUtensorMap to_x, to_xq, to_x1, to_x1q;          // outputs of the GEMMs with fused LayerNorm (box 64 x 32)
     CUtensorMap tr_x, tr_x1;                         // residual maps (box 64 x 32, epilogue TMA loads)
-    static const int kSlots = 2;
-    int32_t * d_ids[kSlots] = {nullptr, nullptr};    // [t_cap]
-    int32_t * d_cu[kSlots] = {nullptr, nullptr};     // [b_cap+1]
-    float * d_out[kSlots] = {nullptr, nullptr};      // [b_cap][H] f32
-    int32_t * h_ids[kSlots] = {nullptr, nullptr};    // pinned mirrors
-    int32_t * h_cu[kSlots] = {nullptr, nullptr};
-    float * h_out[kSlots] = {nullptr, nullptr};
-    cudaEvent_t slot_done[kSlots] = {nullptr, nullptr};
+    static const int kSlots = 3;
+    int32_t * d_ids[kSlots] = {};                    // [t_cap]
+    int32_t * d_cu[kSlots] = {};                     // [b_cap+1]
+    float * d_out[kSlots] = {};                      // [b_cap][H] f32
+    int32_t * h_ids[kSlots] = {};                    // pinned mirrors
+    int32_t * h_cu[kSlots] = {};
+    float * h_out[kSlots] = {};
+    cudaEvent_t h2d_done[kSlots] = {}, fwd_done[kSlots] = {}, slot_done[kSlots] = {};
+    int slot_ready[kSlots] = {};                     // set by the D2H-done host callback (guarded by Engine::q_mu)
+    alignas(8) unsigned char cb_store[kSlots][32] = {};   // argument blocks of those callbacks
 
     // staged job (bertx_stage / bertx_run_staged)
     std::vector<MicroBatch> job_mbs;
@@ -91,6 +136,7 @@ struct Engine {
 
     ~Engine();
     bool init_devices(const ModelFile & mf);
+    void init_limits();
     bool upload(Replica & r, const ModelFile & mf);
     bool alloc_workspace(Replica & r);
     void free_job(Replica & r);
@@ -102,11 +148,36 @@ struct Engine {
     // order sentences by length (descending) and cut into micro-batches
     void plan(const int32_t * n_tokens, int n, std::vector<int> & order, std::vector<MicroBatch> & mbs) const;
 
-    // full host path: token lists -> embeddings scattered to caller pointers
+    // ---- host runtime (pipeline.cu): persistent per-GPU worker threads fed by one queue of micro-batches
+    // bert_forward_batch: token lists -> embeddings scattered to caller pointers
     bool run_tokens(const int32_t * const * tokens, const int32_t * n_tokens, int n, float * const * out);
-    bool run_on_replica(Replica & r, const std::vector<int> & order, const std::vector<MicroBatch> & mbs,
-                        const std::vector<int> & mine, const int32_t * const * tokens, const int32_t * n_tokens,
-                        float * const * out);
+    // bert_encode_batch: texts -> tokenizer pool -> micro-batches -> GPUs, all stages overlapped
+    bool encode_texts(int n_threads, int n, const char ** texts, float ** out);
+    // cut sentences (indices `order`, already sorted by length) into tasks of at most `budget` tokens
+    void cut_tasks(const std::vector<int> & order, const int32_t * const * tok, const int32_t * len, float * const * out,
+                   int budget, const std::shared_ptr<void> & keep, JobState * job, std::vector<MbTask> & tasks) const;
+    // micro-batch token budget for a group of `tokens` tokens over nd GPUs, and the token target of the k-th chunk of a
+    // bert_encode_batch call (small first chunks start the GPUs early); both functions of the counts only
+    int piece_budget(int64_t tokens, int64_t nd) const;
+    int64_t chunk_target(int chunk_no, int64_t nd) const;
+    static constexpr int kTokBlock = 16;          // sentences per tokenizer work item; chunks end on block boundaries
+    // the micro-batches bert_encode_batch would cut for these token counts on nd GPUs (host only; bertx_plan)
+    int plan_encode(const int32_t * n_tokens, int n, int nd, int32_t * mb_of_sentence, std::vector<int> & mb_tokens) const;
+    void submit(std::vector<MbTask> & tasks, JobState & job);
+    void wait_job(JobState & job);
+    bool run_inline(Replica & r, MbTask & t);     // latency path: one micro-batch on the calling thread
+    void start_workers();
+    void stop_workers();
+    void gpu_worker(int ri);
+    bool slot_submit(Replica & r, int s, MbTask & t, bool notify);
+    void slot_retire(Replica & r, int s, MbTask & t, bool ok);
+
+    std::vector<std::thread> workers;
+    std::mutex q_mu;
+    std::condition_variable q_cv;
+    std::deque<MbTask> queue;
+    bool stopping = false;
+    HostPool pool;
 };
 
 bool cuda_ok(cudaError_t e, const char * what);

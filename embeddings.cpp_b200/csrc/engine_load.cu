@@ -140,17 +140,32 @@ bool build_weight(Replica & r, DevWeight & w, const TensorEntry * const * parts,
 }  // namespace
 
 Engine::~Engine() {
+    stop_workers();
     for (Replica & r : reps) {
         if (r.device < 0) continue;
         cudaSetDevice(r.device);
         if (r.stream) cudaStreamSynchronize(r.stream);
         free_job(r);
         for (Replica::Span & s : r.spans) { cudaEventDestroy(s.a); cudaEventDestroy(s.b); }
-        for (int i = 0; i < Replica::kSlots; ++i) if (r.slot_done[i]) cudaEventDestroy(r.slot_done[i]);
+        for (int i = 0; i < Replica::kSlots; ++i) {
+            if (r.slot_done[i]) cudaEventDestroy(r.slot_done[i]);
+            if (r.h2d_done[i]) cudaEventDestroy(r.h2d_done[i]);
+            if (r.fwd_done[i]) cudaEventDestroy(r.fwd_done[i]);
+        }
         for (void * p : r.allocs) cudaFree(p);
         for (void * p : r.pinned) cudaFreeHost(p);
+        if (r.copy_in) { cudaStreamSynchronize(r.copy_in); cudaStreamDestroy(r.copy_in); }
+        if (r.copy_out) { cudaStreamSynchronize(r.copy_out); cudaStreamDestroy(r.copy_out); }
         if (r.stream) cudaStreamDestroy(r.stream);
     }
+}
+
+// micro-batch limits (also valid for a host-only context: the planner is testable without a GPU)
+void Engine::init_limits() {
+    t_cap = 131072;
+    if (const char * e = getenv("BERT_MICROBATCH_TOKENS")) { int v = atoi(e); if (v >= hp.n_max_tokens) t_cap = v; }
+    if (t_cap < hp.n_max_tokens) t_cap = hp.n_max_tokens;
+    b_cap = t_cap / 2 < 16384 ? t_cap / 2 : 16384;                // every sentence has >= 2 ids
 }
 
 bool Engine::init_devices(const ModelFile & mf) {
@@ -186,13 +201,10 @@ bool Engine::init_devices(const ModelFile & mf) {
     if (const char * e = getenv("BERT_ATTN_IMPL")) { attn_ref = strcmp(e, "ref") == 0; attn_mma = strcmp(e, "mma") == 0; }
     fq_type = (hp.ftype == W_Q4_0 || hp.ftype == W_Q4_1) ? hp.ftype : -1;
     if (const char * e = getenv("BERT_ACT_QUANT")) { if (atoi(e) == 0) fq_type = -1; }
-    t_cap = 131072;
+    init_limits();
     if (const char * e = getenv("BERT_POOLING")) pooling = strcmp(e, "cls") == 0 ? 1 : 0;
     if (const char * e = getenv("BERT_SMALL_T")) small_t = atoi(e);
     if (const char * e = getenv("BERT_GELU_H2")) gelu_h2 = atoi(e) != 0;
-    if (const char * e = getenv("BERT_MICROBATCH_TOKENS")) { int v = atoi(e); if (v >= hp.n_max_tokens) t_cap = v; }
-    if (t_cap < hp.n_max_tokens) t_cap = hp.n_max_tokens;
-    b_cap = t_cap / 2 < 16384 ? t_cap / 2 : 16384;                // every sentence has >= 2 ids
 
     reps.resize(devs.size());
     for (size_t i = 0; i < devs.size(); ++i) {
@@ -208,10 +220,13 @@ bool Engine::init_devices(const ModelFile & mf) {
         }
         r.num_sms = prop.multiProcessorCount;
         if (!cuda_ok(cudaStreamCreateWithFlags(&r.stream, cudaStreamNonBlocking), "cudaStreamCreate")) return false;
+        if (!cuda_ok(cudaStreamCreateWithFlags(&r.copy_in, cudaStreamNonBlocking), "cudaStreamCreate")) return false;
+        if (!cuda_ok(cudaStreamCreateWithFlags(&r.copy_out, cudaStreamNonBlocking), "cudaStreamCreate")) return false;
         if (!upload(r, mf)) return false;
         if (!alloc_workspace(r)) return false;
         if (!cuda_ok(cudaStreamSynchronize(r.stream), "upload sync")) return false;
     }
+    start_workers();
     return true;
 }
 
@@ -353,7 +368,9 @@ bool Engine::alloc_workspace(Replica & r) {
         r.h_cu[s] = pinned_alloc<int32_t>(r, b_cap + 1);
         r.h_out[s] = pinned_alloc<float>(r, (size_t) b_cap * H);
         if (!r.d_ids[s] || !r.d_cu[s] || !r.d_out[s] || !r.h_ids[s] || !r.h_cu[s] || !r.h_out[s]) return false;
-        if (!cuda_ok(cudaEventCreateWithFlags(&r.slot_done[s], cudaEventDisableTiming), "cudaEventCreate")) return false;
+        if (!cuda_ok(cudaEventCreateWithFlags(&r.slot_done[s], cudaEventDisableTiming | cudaEventBlockingSync), "cudaEventCreate")) return false;
+        if (!cuda_ok(cudaEventCreateWithFlags(&r.h2d_done[s], cudaEventDisableTiming), "cudaEventCreate")) return false;
+        if (!cuda_ok(cudaEventCreateWithFlags(&r.fwd_done[s], cudaEventDisableTiming), "cudaEventCreate")) return false;
     }
     return true;
 }

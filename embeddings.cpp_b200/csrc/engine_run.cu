@@ -1,6 +1,5 @@
-// The encoder forward as a fixed sequence of sm_100a kernels on one stream per GPU, and
-// the host scheduler that feeds it (length sort, token-budget micro-batches, sharding of
-// micro-batches over the GPUs with no collective, pinned double-buffered staging).
+// The encoder forward as a fixed sequence of sm_100a kernels on one stream per GPU (the host
+// runtime that feeds it -- tokenizer pool, micro-batch queue, per-GPU workers -- is pipeline.cu).
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
@@ -128,98 +127,6 @@ void Engine::plan(const int32_t * n_tokens, int n, std::vector<int> & order, std
         off += len;
     }
     if (cur.count > 0) mbs.push_back(cur);
-}
-
-bool Engine::run_on_replica(Replica & r, const std::vector<int> & order, const std::vector<MicroBatch> & mbs,
-                            const std::vector<int> & mine, const int32_t * const * tokens, const int32_t * n_tokens,
-                            float * const * out) {
-    if (!cuda_ok(cudaSetDevice(r.device), "cudaSetDevice")) return false;
-    const int H = hp.n_embd;
-    bool ok = true;
-    int pending[Replica::kSlots] = {-1, -1};          // micro-batch whose results sit in the slot
-    auto drain = [&](int s) {
-        if (pending[s] < 0) return;
-        if (!cuda_ok(cudaEventSynchronize(r.slot_done[s]), "slot sync")) { ok = false; pending[s] = -1; return; }
-        const MicroBatch & mb = mbs[pending[s]];
-        for (int i = 0; i < mb.count; ++i) {
-            memcpy(out[order[mb.first + i]], r.h_out[s] + (size_t) i * H, (size_t) H * sizeof(float));
-        }
-        pending[s] = -1;
-    };
-    for (size_t k = 0; k < mine.size() && ok; ++k) {
-        const int s = (int) (k % Replica::kSlots);
-        drain(s);
-        if (!ok) break;
-        const MicroBatch & mb = mbs[mine[k]];
-        int32_t * ids = r.h_ids[s];
-        int32_t * cu = r.h_cu[s];
-        int t = 0;
-        for (int i = 0; i < mb.count; ++i) {
-            const int idx = order[mb.first + i];
-            cu[i] = t;
-            memcpy(ids + t, tokens[idx], (size_t) n_tokens[idx] * sizeof(int32_t));
-            t += n_tokens[idx];
-        }
-        cu[mb.count] = t;
-        ok = ok && cuda_ok(cudaMemcpyAsync(r.d_ids[s], ids, (size_t) t * 4, cudaMemcpyHostToDevice, r.stream), "H2D ids");
-        ok = ok && cuda_ok(cudaMemcpyAsync(r.d_cu[s], cu, (size_t) (mb.count + 1) * 4, cudaMemcpyHostToDevice, r.stream), "H2D cu");
-        ok = ok && forward(r, r.d_ids[s], r.d_cu[s], mb.count, t, mb.max_len, r.d_out[s]);
-        ok = ok && cuda_ok(cudaMemcpyAsync(r.h_out[s], r.d_out[s], (size_t) mb.count * H * 4, cudaMemcpyDeviceToHost, r.stream), "D2H out");
-        ok = ok && cuda_ok(cudaEventRecord(r.slot_done[s], r.stream), "event record");
-        if (ok) pending[s] = mine[k];
-    }
-    for (int s = 0; s < Replica::kSlots; ++s) drain(s);
-    if (!ok) cudaStreamSynchronize(r.stream);
-    const cudaError_t e = cudaGetLastError();
-    return ok && e == cudaSuccess;
-}
-
-bool Engine::run_tokens(const int32_t * const * tokens, const int32_t * n_tokens, int n, float * const * out) {
-    if (n <= 0) return true;
-    if (reps.empty()) {
-        fprintf(stderr, "libbert(b200): this context has no GPU replica (host-only load); there is no CPU path\n");
-        return false;
-    }
-    for (int i = 0; i < n; ++i) {
-        if (n_tokens[i] > hp.n_max_tokens) {                  // reference bert.cpp:867-871
-            fprintf(stderr, "Too many tokens, maximum is %d\n", hp.n_max_tokens);
-            return false;
-        }
-        if (n_tokens[i] <= 0) {
-            fprintf(stderr, "bert_forward_batch: input %d has no tokens\n", i);
-            return false;
-        }
-    }
-    std::vector<int> order;
-    std::vector<MicroBatch> mbs;
-    plan(n_tokens, n, order, mbs);
-    const int H = hp.n_embd, I = hp.n_intermediate;
-    // longest-processing-time assignment of micro-batches to GPUs (cost ~ FLOPs)
-    const size_t nd = reps.size();
-    std::vector<std::vector<int>> mine(nd);
-    std::vector<double> load(nd, 0.0);
-    std::vector<int> by_cost(mbs.size());
-    std::iota(by_cost.begin(), by_cost.end(), 0);
-    auto cost = [&](const MicroBatch & m) {
-        return (double) m.tokens * (8.0 * H * H + 4.0 * H * I) + 4.0 * (double) m.tokens * m.max_len * H;
-    };
-    std::stable_sort(by_cost.begin(), by_cost.end(), [&](int a, int b) { return cost(mbs[a]) > cost(mbs[b]); });
-    for (int m : by_cost) {
-        const size_t d = std::min_element(load.begin(), load.end()) - load.begin();
-        mine[d].push_back(m);
-        load[d] += cost(mbs[m]);
-    }
-    // temporaries in a failed call must not leak into caller buffers: results are only
-    // scattered per finished micro-batch; on failure the remaining outputs stay untouched.
-    if (nd == 1) return run_on_replica(reps[0], order, mbs, mine[0], tokens, n_tokens, out);
-    std::vector<std::thread> th;
-    std::vector<char> oks(nd, 1);
-    for (size_t d = 0; d < nd; ++d) {
-        if (mine[d].empty()) continue;
-        th.emplace_back([&, d]() { oks[d] = run_on_replica(reps[d], order, mbs, mine[d], tokens, n_tokens, out) ? 1 : 0; });
-    }
-    for (auto & t : th) t.join();
-    return std::all_of(oks.begin(), oks.end(), [](char c) { return c != 0; });
 }
 
 void Engine::free_job(Replica & r) {

@@ -27,28 +27,25 @@ constexpr int kSmemLimit = 232448;                   // 227 KB opt-in limit per 
 // EPB (fused LayerNorm, short K): the epilogue chain (residual load -> pass 1 -> statistics exchange -> pass 2 ->
 // stores) is longer than the mainloop of a tile, so smem goes to the epilogue instead of the rings: the q8 twin
 // gets its own staging buffer and the residual box of the NEXT tile is fetched while this tile is normalised.
-#ifndef BERT_DQ_LDS_SINK
-#define BERT_DQ_LDS_SINK 0
+// Build-time knobs kept from the round-2 bisect of the mainloop race (profiles/r2_gemm_race.md); the defaults are the
+// shipped kernel, the other values exist so that the regression experiment can be repeated:
+//   BERT_NIB_HANDBACK  when the dequant warps hand a 4-bit slot back to the bulk-copy warp:
+//       2 (default)  at the end of the stage, after the slot's words have gone through the dequant arithmetic and the
+//                    stores' MEMBAR -- the refill can then never land before a shared load has read the slot
+//       0            right after ISSUING the shared loads (round 1).  This is the race: the refill of the slot (the
+//                    stage 6 ahead) can land before a load has read it, and the warp dequantises the wrong stage.
+//       3 / 4        after a fence.acq_rel.cta / after a named barrier of the warp group (both also close the race)
+//   BERT_EPI_LDX       1 (default) both 32-column halves of an epilogue box are loaded from TMEM up front; 0: one at a time
+//   BERT_DQ_SYNC       0 (default) __syncwarp + lane 0 publishes a dequantised B stage; 1: every thread arrives itself
+//   BERT_GEMM_SA / BERT_GEMM_SB   ring depths of the plain q4 instantiations (timing perturbations for the tests)
+#ifndef BERT_NIB_HANDBACK
+#define BERT_NIB_HANDBACK 2
 #endif
 #ifndef BERT_EPI_LDX
-#define BERT_EPI_LDX 0
+#define BERT_EPI_LDX 1
 #endif
-// diagnostic knobs for the epilogue item of profiles/r2_gemm_race.md (defaults = the shipped kernel)
-#ifndef BERT_XCTA_RELEASE
-#define BERT_XCTA_RELEASE 0      // 1: cross-CTA arrives (b_full, tempty) release at cluster scope, MMA-side waits acquire at cluster scope
-#endif
-#ifndef BERT_EPI_STORE_WAIT_ALL
-#define BERT_EPI_STORE_WAIT_ALL 0  // 1: the staging buffer is only reused after the previous TMA store completed its global writes
-#endif
-#ifndef BERT_EPI_DELAY_NS
-#define BERT_EPI_DELAY_NS 0        // > 0: every epilogue warp sleeps this long before it hands the accumulator back
-#endif
-#if BERT_EPI_LDX == 2
-// diagnostic: [0] words whose early read (both halves up front) differs from the late re-read, [1] words compared
-__device__ unsigned long long g_epi_ld_diag[2];
-extern "C" __attribute__((visibility("default"))) int bertx_debug_epi_ld(unsigned long long * out2) {
-    return (int) cudaMemcpyFromSymbol(out2, g_epi_ld_diag, sizeof(g_epi_ld_diag));
-}
+#ifndef BERT_DQ_SYNC
+#define BERT_DQ_SYNC 0
 #endif
 template <int BN, int WT, bool LN, bool RES, bool EPB = false> struct GemmCfg {
     static constexpr bool kQ4      = WT != W_F16;
@@ -266,7 +263,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         if (RES) tma_prefetch_desc(&tmap_res);
         for (int s = 0; s < SA; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
         if (Q4) {
-            for (int s = 0; s < SB; ++s) { mbar_init(&b_full[s], 2 * DQ_GROUP_WARPS); mbar_init(&b_empty[s], 1); }
+            for (int s = 0; s < SB; ++s) { mbar_init(&b_full[s], 2 * DQ_GROUP_WARPS * (BERT_DQ_SYNC == 1 ? 32 : 1)); mbar_init(&b_empty[s], 1); }
             for (int s = 0; s < SN; ++s) { mbar_init(&n_full[s], 1); mbar_init(&n_empty[s], DQ_GROUP_WARPS); }
         }
         for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 2 * EPI_WARPS); }
@@ -311,20 +308,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             for (int it = 0; it < my_tiles; ++it) {
                 const int acc = it & 1;
                 const uint32_t acc_ph = (it >> 1) & 1;
-#if BERT_XCTA_RELEASE
-                mbar_wait_cluster_acquire(&tempty[acc], acc_ph ^ 1);
-#else
                 mbar_wait(&tempty[acc], acc_ph ^ 1);
-#endif
                 tc_fence_after_sync();
                 const uint32_t d_tmem = tmem_base + acc * Cfg::kAccStride;
                 for (int kb = 0; kb < num_k; ++kb) {
                     mbar_wait(&a_full[sa], pha);
-#if BERT_XCTA_RELEASE
-                    if (Q4) mbar_wait_cluster_acquire(&b_full[sb], phb);
-#else
                     if (Q4) mbar_wait(&b_full[sb], phb);
-#endif
                     tc_fence_after_sync();
                     if (elect_one()) {
                         const uint64_t adesc = umma_smem_desc_sw128(smem_u32(smem_a + sa * Cfg::kABytes));
@@ -425,7 +414,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 mbar_wait(rbar, rph); rph ^= 1;
 #pragma unroll
                 for (int c = 0; c < 8; ++c) rr[c] = *reinterpret_cast<const uint4 *>(rs + lane * 128 + ((c ^ (lane & 7)) << 4));
-                uint32_t sink; asm volatile("mov.b32 %0, %1;" : "=r"(sink) : "r"(rr[7].w));
+                fence_loads_done();                           // before the buffer goes back to the TMA (see the plain epilogue)
                 __syncwarp();
                 if (bi + 1 < NBW && lane == 0) {              // this tile's next box
                     mbar_expect_tx(rbar, 4096);
@@ -614,8 +603,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     mbar_wait(rbar, j & 1);
 #pragma unroll
                     for (int c = 0; c < 8; ++c) rr[c] = *reinterpret_cast<const uint4 *>(rs + lane * 128 + ((c ^ (lane & 7)) << 4));
-                    // force the last shared load to have landed before the buffer is handed back to the TMA
-                    uint32_t sink; asm volatile("mov.b32 %0, %1;" : "=r"(sink) : "r"(rr[7].w));
+                    // the shared loads must have COMPLETED (not just issued) before the buffer is handed back to the TMA
+                    // (a register "sink" does not do it: ptxas removes a mov whose result is dead)
+                    fence_loads_done();
                 }
                 __syncwarp();
                 if (j + 1 < total_boxes) {
@@ -626,37 +616,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     }
                     if (has_bias) bnext = __ldg(reinterpret_cast<const float2 *>(p.bias + c1) + lane);
                 }
+                const uint32_t acc_addr = tmem_base + ((uint32_t) (q * 32) << 16) + acc * Cfg::kAccStride + b * 64;
 #if BERT_EPI_LDX
-                // diagnostic builds for the open item in profiles/r1_head.md: 1 = both halves up front, a wait after EACH load
+                // both 32-column halves of the box in flight at once, one wait (1 % faster than one half at a time)
                 uint32_t r2[2][32];
-                tmem_ld_32x32b_x32(tmem_base + ((uint32_t) (q * 32) << 16) + acc * Cfg::kAccStride + b * 64, r2[0]);
-                tmem_ld_wait();
-                tmem_ld_32x32b_x32(tmem_base + ((uint32_t) (q * 32) << 16) + acc * Cfg::kAccStride + b * 64 + 32, r2[1]);
+                tmem_ld_32x32b_x32(acc_addr, r2[0]);
+                tmem_ld_32x32b_x32(acc_addr + 32, r2[1]);
                 tmem_ld_wait();
 #endif
 #pragma unroll
                 for (int hh = 0; hh < 2; ++hh) {
-                    // one 32-column load in flight at a time: loading both halves of the box up front (two loads + one
-                    // tcgen05.wait::ld, also as a single asm statement) measured 1 % faster but gave NON-DETERMINISTIC
-                    // results at full size (tests/test_gpu.py::test_full_size_properties_bge_base failed 7 of 7 runs,
-                    // this form 0 of 7; kernel self-tests pass either way).  Root cause open: profiles/r1_head.md
-#if BERT_EPI_LDX == 1
+#if BERT_EPI_LDX
                     const uint32_t * r = r2[hh];
-#elif BERT_EPI_LDX == 2
-                    // compute from the LATE read (the shipped order); count where the early read disagrees with it
-                    uint32_t r[32];
-                    tmem_ld_32x32b_x32(tmem_base + ((uint32_t) (q * 32) << 16) + acc * Cfg::kAccStride + b * 64 + hh * 32, r);
-                    tmem_ld_wait();
-                    {
-                        unsigned bad = 0;
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) bad += (r[i] != r2[hh][i]) ? 1u : 0u;
-                        if (bad) atomicAdd(&g_epi_ld_diag[0], (unsigned long long) bad);
-                        if (lane == 0 && hh == 1) atomicAdd(&g_epi_ld_diag[1], 2048ull);
-                    }
 #else
                     uint32_t r[32];
-                    tmem_ld_32x32b_x32(tmem_base + ((uint32_t) (q * 32) << 16) + acc * Cfg::kAccStride + b * 64 + hh * 32, r);
+                    tmem_ld_32x32b_x32(acc_addr + hh * 32, r);
                     tmem_ld_wait();
 #endif
                     float2 v[16];
@@ -688,11 +662,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     if (p.epilogue & EPI_FAKEQUANT) fake_quant32_v2(v, p.fq_type);
                     if (hh == 0) {
                         // the TMA store of this warp's previous box must be done reading the staging buffer
-#if BERT_EPI_STORE_WAIT_ALL
-                        if (lane == 0) tma_store_wait_all<0>();
-#else
                         if (lane == 0) tma_store_wait_read<0>();
-#endif
                         __syncwarp();
                     }
 #pragma unroll
@@ -714,14 +684,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             }
             tc_fence_before_sync();
             __syncwarp();
-#if BERT_EPI_DELAY_NS > 0
-            __nanosleep(BERT_EPI_DELAY_NS);
-#endif
-#if BERT_XCTA_RELEASE
-            if (lane == 0) mbar_arrive_cluster_release(tempty_leader + 8 * acc);
-#else
             if (lane == 0) mbar_arrive_cluster(tempty_leader + 8 * acc);
-#endif
         }
         if (lane == 0) tma_store_wait_all<0>();
       }
@@ -754,14 +717,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         m[u] = WT == W_Q4_1 ? *reinterpret_cast<const __half *>(slot + Cfg::kNibBytes + Cfg::kScaleBytes + unit * 2) : __half();
                     }
                 }
-#if BERT_DQ_LDS_SINK
-                {   // the shared loads above must have LANDED (not just issued) before the slot is handed back to the bulk copy
-                    uint32_t sink;
-                    asm volatile("mov.b32 %0, %1;" : "=r"(sink) : "r"(nib[UNITS - 1].w ^ (uint32_t) __half_as_ushort(d[UNITS - 1]) ^ (uint32_t) __half_as_ushort(m[UNITS - 1])));
-                }
+                // Handing the 4-bit slot back: NOT here.  The loads above are only issued at this point; arriving on n_empty now
+                // lets the bulk-copy warp refill the slot (with the stage SN ahead) before a load has read it -- seen on B200
+                // as 16-column groups of a tile carrying the weights of the stage 6 ahead (profiles/r2_gemm_race.md).
+#if BERT_NIB_HANDBACK == 3
+                fence_loads_done();
+#elif BERT_NIB_HANDBACK == 4
+                named_bar_sync(2 + grp, GT);
 #endif
+#if BERT_NIB_HANDBACK != 2
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&n_empty[sn]);            // slot may be refilled
+                if (lane == 0) mbar_arrive(&n_empty[sn]);
+#endif
                 // dequantise into registers first (one 32-weight unit at a time: the register budget of these warps is small):
                 // only the stores of the first batch sit between "slot free" and "slot full"
                 constexpr int UB = 1;
@@ -796,11 +763,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     }
                 }
                 fence_proxy_async_smem();
-                __syncwarp();
-#if BERT_XCTA_RELEASE
-                if (lane == 0) mbar_arrive_cluster_release(bfull_leader + 8 * sb);
+#if BERT_DQ_SYNC == 1
+                mbar_arrive_cluster(bfull_leader + 8 * sb);          // every thread publishes its own stores
 #else
+                __syncwarp();
                 if (lane == 0) mbar_arrive_cluster(bfull_leader + 8 * sb);
+#endif
+#if BERT_NIB_HANDBACK == 2
+                // every word loaded from the slot has gone through the dequant arithmetic into the stores above, and the
+                // proxy fence's MEMBAR has completed: the slot is certainly read, hand it back
+                if (lane == 0) mbar_arrive(&n_empty[sn]);
 #endif
                 sn += DQ_GROUPS; if (sn >= SN) { sn -= SN; phn ^= 1; }
                 sb += DQ_GROUPS; if (sb >= SB) { sb -= SB; phb ^= 1; }

@@ -73,6 +73,12 @@ __device__ __forceinline__ void mbar_wait(uint64_t * bar, uint32_t parity) {
     }
 }
 
+// All shared / global loads this thread has issued have COMPLETED when this returns (MEMBAR.ALL.CTA).  Needed before a
+// buffer the thread has just read is handed to an async-proxy writer (TMA / bulk copy): an mbarrier arrive right after the
+// loads only orders their ISSUE, and a "sink" mov of a loaded register is removed by ptxas as dead code.
+__device__ __forceinline__ void fence_loads_done() {
+    asm volatile("fence.acq_rel.cta;" ::: "memory");
+}
 // generic-proxy smem writes -> visible to the async proxy (UMMA / TMA reads)
 __device__ __forceinline__ void fence_proxy_async_smem() {
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");

@@ -33,6 +33,13 @@ BERT_API int64_t bertx_tokenize_batch(struct bert_ctx * ctx, int32_t n_threads, 
                                       const char ** texts, bert_vocab_id * tokens_out, int64_t cap,
                                       int32_t * n_tokens_out);
 
+/* The micro-batches one bert_encode_batch call would cut for sentences of these token counts on n_devices GPUs (the
+ * scheduler of reference bert.cpp:1394-1443 re-designed: deterministic chunks on 16-sentence boundaries, sorted by
+ * length, packed to a token budget; any GPU takes the next micro-batch).  Works on a host-only context.  Writes the
+ * micro-batch index of every sentence and the token count of every micro-batch (capacity cap); returns their number. */
+BERT_API int32_t bertx_plan(struct bert_ctx * ctx, int32_t n_devices, int32_t n_sent, const int32_t * n_tokens,
+                            int32_t * mb_of_sentence, int32_t * mb_tokens, int32_t cap);
+
 /* Stage a whole job on device `dev` (index into the context's device list): packed ids
  * + lengths are copied to HBM and cut into micro-batches.  Returns 0 on success. */
 BERT_API int32_t bertx_stage(struct bert_ctx * ctx, int32_t dev, int32_t n_sent,
@@ -79,9 +86,12 @@ BERT_API int32_t bertx_bench_attention(int32_t n_sent, int32_t len, int32_t n_he
 
 /* Debug aid for kernel bisects: one GEMM of ANY size on device-generated operands; the SIMT validation kernel's output
  * and `runs` outputs of the tcgen05 kernel ([M][N] fp16 bit patterns each) are copied to host arrays the caller owns,
- * ms_tc[runs] receives the kernel times.  Fused-LayerNorm epilogues are not supported here. */
+ * ms_tc[runs] receives the kernel times.  out_ref NULL: no validation run.  out_ref2 / out_tc2 (may be NULL): the q8 twin
+ * a fused-LayerNorm epilogue (bit4) writes; a_out / w_out (may be NULL): the A operand ([M][K] fp16 bits) and the weights as
+ * the kernels decode them ([N][K] f32). */
 BERT_API int32_t bertx_debug_gemm(int32_t M, int32_t N, int32_t K, int32_t wtype, int32_t epilogue, int32_t seed,
-                                  int32_t runs, uint16_t * out_ref, uint16_t * out_tc, float * ms_tc);
+                                  int32_t runs, uint16_t * out_ref, uint16_t * out_tc, float * ms_tc,
+                                  uint16_t * out_ref2, uint16_t * out_tc2, uint16_t * a_out, float * w_out);
 
 /* Model quantiser: fname_inp (f32 / f16 file) -> fname_out with every 2-D "*weight" tensor as
  * q4_0 (itype 2) or q4_1 (itype 3) blocks, byte-identical to the reference's `quantize` tool

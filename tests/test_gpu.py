@@ -244,6 +244,42 @@ def test_full_size_properties_bge_base(pkg):
     m.close()
 
 
+def test_full_size_determinism_under_perturbed_builds(pkg, tmp_path):
+    """The round-2 mainloop race (profiles/r2_gemm_race.md) only showed when the timing of the GEMM CTA shifted, so
+    the full-size check also runs on three timing-perturbed builds of the kernel (build.py PERTURBED: one epilogue TMEM load
+    at a time / every dequant thread arrives itself / rings one stage shorter) and with PDL off.  None of them changes
+    the arithmetic: every build must give the default build's embeddings bit for bit, twice in a row."""
+    import subprocess
+    import sys
+    libs = {"default": pkg.LIB_PATH}
+    for path in pkg.build_perturbed():
+        libs[os.path.basename(path)[len("libbert_"):-3]] = path
+    script = (
+        "import sys, numpy as np\n"
+        f"sys.path.insert(0, {os.path.dirname(os.path.dirname(os.path.abspath(__file__)))!r})\n"
+        "import __graft_entry__ as ge\n"
+        "from tools import synth\n"
+        "pkg = ge.load_package()\n"
+        "m = pkg.BertModel(synth.model_path('bge-base-en-v1.5', 'q4_0'))\n"
+        "texts = synth.texts_exact_len(synth.make_vocab(30522, 0), 512, 512, seed=0)\n"
+        "e = m.encode(texts)\n"
+        "assert np.array_equal(m.encode(texts), e), 'run-to-run difference'\n"
+        "np.save(sys.argv[1], e)\n")
+    runs = [(name, {}) for name in libs] + [("default", {"BERT_PDL": "0"})]
+    want = None
+    for i, (name, extra) in enumerate(runs):
+        out = str(tmp_path / f"e{i}.npy")
+        env = dict(os.environ, BERT_B200_LIB=libs[name], **extra)
+        r = subprocess.run([sys.executable, "-c", script, out], env=env, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, (name, extra, r.stdout[-400:], r.stderr[-800:])
+        e = np.load(out)
+        assert np.isfinite(e).all()
+        if want is None:
+            want = e
+        else:
+            assert np.array_equal(e, want), (name, extra, float(np.abs(e - want).max()))
+
+
 def test_in_process_sharding_over_all_visible_gpus(pkg):
     """One process, every visible GPU (what a drop-in caller of bert_encode_batch gets on a multi-GPU box):
     micro-batches are dealt to the replicas with no collective; results equal the single-GPU ones bit for bit."""
