@@ -73,6 +73,8 @@ def lib():
     L.bertx_set_pooling.argtypes = [vp, c_i32]
     L.bertx_kernel_launches.restype = c_i64
     L.bertx_kernel_launches.argtypes = [vp]
+    L.bertx_plan.restype = c_i32
+    L.bertx_plan.argtypes = [vp, c_i32, c_i32, pi, pi, pi, c_i32]
     L.bertx_tokenize_batch.restype = c_i64
     L.bertx_tokenize_batch.argtypes = [vp, c_i32, c_i32, ctypes.POINTER(cp), pi, c_i64, pi]
     L.bertx_stage.restype = c_i32
@@ -187,6 +189,17 @@ class BertModel:
 
     def kernel_launches(self):
         return int(self.lib.bertx_kernel_launches(self.ctx))
+
+    def plan(self, lens, n_devices=1):
+        """The micro-batches one encode() call would cut for sentences of these token counts on n_devices GPUs
+        (bertx_plan; works on a host-only context).  Returns (micro-batch index per sentence, tokens per micro-batch)."""
+        lens = np.ascontiguousarray(lens, dtype=np.int32)
+        mb_of = np.zeros(len(lens), dtype=np.int32)
+        mb_tok = np.zeros(len(lens) + 1, dtype=np.int32)
+        n = self.lib.bertx_plan(self.ctx, n_devices, len(lens), _ip(lens), _ip(mb_of), _ip(mb_tok), len(mb_tok))
+        if n < 0:
+            raise RuntimeError(f"bertx_plan failed ({n})")
+        return mb_of, mb_tok[:n].copy()
 
     def tokenize_batch(self, sentences):
         n = len(sentences)

@@ -103,6 +103,7 @@ struct bert_ctx * bert_load_from_file(const char * fname) {
         printf("%s: model size = %8.2f MB / num tensors = %d\n", __func__, mf.total_tensor_bytes / 1024.0 / 1024.0, mf.n_tensors);
         printf("%s: %zu x sm_100a replica(s), micro-batch %d tokens, activation quant emulation %s\n", __func__,
                ctx->eng.reps.size(), ctx->eng.t_cap, ctx->eng.fq_type >= 0 ? "on" : "off");
+        if (mf.hp.ftype == 0) printf("%s: f32 weights are held as fp16 on the device (fp16 operands, f32 accumulation)\n", __func__);
         fflush(stdout);
         return ctx;
     } catch (const std::exception & ex) {

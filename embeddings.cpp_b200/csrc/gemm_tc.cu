@@ -96,6 +96,13 @@ struct GemmParams {
     int M, N, K, epilogue, fq_type;
 };
 
+// Two floats -> packed fp16 pair (x in the low half), SATURATING to +-65504: the reference keeps f32 activations, so an
+// outlier above the fp16 range must not become inf here (inf * 0 in a later masked P V product would poison a sentence)
+__device__ __forceinline__ __half2 pack_h2_sat(float x, float y) {
+    uint32_t r;
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(y), "f"(x));
+    return *reinterpret_cast<__half2 *>(&r);
+}
 __device__ __forceinline__ float ex2_approx(float x) {
     float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y;
 }
@@ -437,7 +444,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         float2 v1 = make_float2(__uint_as_float(r[4 * i + 2]), __uint_as_float(r[4 * i + 3]));
                         v0 = __fadd2_rn(__fadd2_rn(v0, make_float2(bb.x, bb.y)), r0);
                         v1 = __fadd2_rn(__fadd2_rn(v1, make_float2(bb.z, bb.w)), r1);
-                        __half2 a0 = __floats2half2_rn(v0.x, v0.y), a1 = __floats2half2_rn(v1.x, v1.y);
+                        __half2 a0 = pack_h2_sat(v0.x, v0.y), a1 = pack_h2_sat(v1.x, v1.y);
                         hv[bi][hh * 16 + 2 * i] = *reinterpret_cast<uint32_t *>(&a0);
                         hv[bi][hh * 16 + 2 * i + 1] = *reinterpret_cast<uint32_t *>(&a1);
                     }
@@ -522,7 +529,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         uint4 u;
                         __half2 * h = reinterpret_cast<__half2 *>(&u);
 #pragma unroll
-                        for (int k = 0; k < 4; ++k) h[k] = __floats2half2_rn(v[i * 4 + k].x, v[i * 4 + k].y);
+                        for (int k = 0; k < 4; ++k) h[k] = pack_h2_sat(v[i * 4 + k].x, v[i * 4 + k].y);
                         *reinterpret_cast<uint4 *>(st + lane * 128 + ((c ^ (lane & 7)) << 4)) = u;
                     }
                     if (fq_on) {
@@ -533,7 +540,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             uint4 u;
                             __half2 * h = reinterpret_cast<__half2 *>(&u);
 #pragma unroll
-                            for (int k = 0; k < 4; ++k) h[k] = __floats2half2_rn(v[i * 4 + k].x, v[i * 4 + k].y);
+                            for (int k = 0; k < 4; ++k) h[k] = pack_h2_sat(v[i * 4 + k].x, v[i * 4 + k].y);
                             *reinterpret_cast<uint4 *>(tws + lane * 128 + ((c ^ (lane & 7)) << 4)) = u;
                         }
                     }
@@ -671,7 +678,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         uint4 u;
                         __half2 * h = reinterpret_cast<__half2 *>(&u);
 #pragma unroll
-                        for (int k = 0; k < 4; ++k) h[k] = __floats2half2_rn(v[i * 4 + k].x, v[i * 4 + k].y);
+                        for (int k = 0; k < 4; ++k) h[k] = pack_h2_sat(v[i * 4 + k].x, v[i * 4 + k].y);
                         *reinterpret_cast<uint4 *>(st + lane * 128 + ((c ^ (lane & 7)) << 4)) = u;
                     }
                 }

@@ -94,7 +94,10 @@ struct Batcher {
             n_requests += batch.size();
             n_batches += 1;
             for (Request * r : batch) {
-                { std::lock_guard<std::mutex> g(r->m); r->done = true; }
+                // notify while holding the lock: the Request lives on the connection thread's stack and may be
+                // destroyed as soon as the waiter can observe done == true
+                std::lock_guard<std::mutex> g(r->m);
+                r->done = true;
                 r->cv.notify_one();
             }
         }
@@ -178,16 +181,14 @@ int main(int argc, char ** argv) {
     printf("Server running on port %d with %d threads\n", (int) ntohs(address.sin_port), params.n_threads);
     fflush(stdout);
 
-    std::vector<std::thread> conns;
     while (true) {
         const int fd = accept(server_fd, nullptr, nullptr);
         if (fd < 0) break;                                  // listening socket shut down by the signal handler
-        conns.emplace_back(serve_connection, fd, &batcher);
+        std::thread(serve_connection, fd, &batcher).detach();   // a connection thread owns nothing the server must reap
     }
     batcher.stop = true;
     batcher.cv.notify_all();
     batch_thread.join();
-    for (auto & t : conns) t.detach();                      // blocked in recv on sockets the clients still hold
     printf("served %llu requests in %llu batches\n", (unsigned long long) batcher.n_requests.load(),
            (unsigned long long) batcher.n_batches.load());
     fflush(stdout);

@@ -223,6 +223,84 @@ def test_named_model_shapes_against_live_reference(pkg, shape, ft, n, lo, hi):
     ref.close()
 
 
+PARITY_LOG = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out", "parity_r2.jsonl")
+
+
+def _record(row):
+    """One line per parity case for the table in DESIGN.md section 4 (written on the GPU box, merged back by gpurun)."""
+    import json
+    try:
+        os.makedirs(os.path.dirname(PARITY_LOG), exist_ok=True)
+        with open(PARITY_LOG, "a") as f:
+            f.write(json.dumps(row) + "\n")
+    except OSError:
+        pass
+
+
+# BASELINE.json's five configs at the sample sizes SURVEY 8(d) / BASELINE.md section 4 name, against the LIVE compiled
+# reference (oracle/_ref/libbert_ref.so, the unmodified ggml CPU path), plus bge-base in f32 and f16 at 512 tokens.
+CONFIG_PARITY = [
+    # id, shape, ftype, text kind, sentences, tokens (0 = variable), reference chunk
+    ("config1-minilm-q4_0-1738-lines", "all-MiniLM-L6-v2", "q4_0", "client", 1738, 0, 16),
+    ("config2-bge-small-f16-256x128", "bge-small-en-v1.5", "f16", "exact", 256, 128, 8),
+    ("config3-bge-base-q4_0-64x512", "bge-base-en-v1.5", "q4_0", "exact", 64, 512, 2),
+    ("config4-bge-small-zh-q4_1-256-var", "bge-small-zh-v1.5", "q4_1", "cjkvar", 256, 0, 8),
+    ("config5-bge-large-q4_0-32x256", "bge-large-en-v1.5", "q4_0", "exact", 32, 256, 4),
+    ("bge-base-f32-8x512", "bge-base-en-v1.5", "f32", "exact", 8, 512, 2),
+    ("bge-base-f16-8x512", "bge-base-en-v1.5", "f16", "exact", 8, 512, 2),
+]
+
+
+@pytest.mark.skipif(not reflib.available(), reason="oracle/_ref did not travel to this box")
+@pytest.mark.parametrize("cid,shape,ft,kind,n,n_tok,chunk", CONFIG_PARITY, ids=[c[0] for c in CONFIG_PARITY])
+def test_baseline_configs_against_live_reference(pkg, cid, shape, ft, kind, n, n_tok, chunk):
+    import bench
+    model = synth.model_path(shape, ft)
+    texts = bench.make_texts(shape, kind, n, n_tok)
+    m = pkg.BertModel(model)
+    got = m.encode(texts)
+    ref = reflib.RefBert(model)
+    toks = [ref.tokenize(t) for t in texts]
+    ids, lens = m.tokenize_batch(texts)
+    assert ids.tolist() == [i for t in toks for i in t]                      # token ids bit-exact on the whole set
+    order = np.argsort([len(t) for t in toks], kind="stable")                # the reference pads to the chunk's longest
+    want = np.zeros_like(got)
+    want[order] = ref.forward_tokens([toks[i] for i in order], chunk=chunk)
+    cos, err = cos_and_maxabs(got, want)
+    _record({"case": cid, "weights": ft, "sentences": n, "tokens": int(lens.sum()), "min_cosine": cos, "max_abs": err})
+    print(f"\n{cid}: min cosine {cos:.7f} max abs {err:.2e}")
+    assert cos >= COS_MIN and err <= MAX_ABS[ft], (cos, err)
+    m.close()
+    ref.close()
+
+
+@pytest.mark.skipif(not reflib.available(), reason="oracle/_ref did not travel to this box")
+@pytest.mark.parametrize("ft", ["f16", "q4_0", "q4_1"])
+def test_outlier_channels_against_live_reference(pkg, ft):
+    """Weights with a few hidden channels at 20-50x the typical LayerNorm gain / bias (what real BERT checkpoints have and
+    the default synthetic weights do not): the fp16 residual stream and the q8 activation twin must still
+    follow the reference's f32 activations."""
+    shape = "bge-base-en-v1.5"
+    model = synth.model_path(shape, ft, outliers=True)
+    vocab = synth.make_vocab(synth.SHAPES[shape][4], 0)
+    texts = synth.texts_var_len(vocab, 10, 8, 300, seed=31)
+    m = pkg.BertModel(model)
+    got = m.encode(texts)
+    ref = reflib.RefBert(model)
+    toks = [ref.tokenize(t) for t in texts]
+    want = ref.forward_tokens(toks, chunk=2)
+    self_check = ref.forward_tokens(toks[:4], chunk=1)                       # the reference against itself, other batching
+    cos, err = cos_and_maxabs(got, want)
+    scos, serr = cos_and_maxabs(self_check, want[:4])
+    _record({"case": "outlier-channels-bge-base", "weights": ft, "sentences": len(texts), "min_cosine": cos, "max_abs": err,
+             "reference_self_min_cosine": scos, "reference_self_max_abs": serr})
+    print(f"\noutlier channels {ft}: min cosine {cos:.7f} max abs {err:.2e} (reference vs itself: {scos:.7f} / {serr:.2e})")
+    assert np.isfinite(got).all()
+    assert cos >= COS_MIN and err <= MAX_ABS[ft], (cos, err)
+    m.close()
+    ref.close()
+
+
 def test_full_size_properties_bge_base(pkg):
     """Size-independent properties at BASELINE's full size (512 x 512 tokens): unit norm,
     permutation equivariance of the batch, duplicate sentences give identical rows."""

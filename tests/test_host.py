@@ -77,6 +77,41 @@ def test_host_tokenizer_fuzz_against_oracle(pkg):
     m.close()
 
 
+@pytest.mark.skipif(not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libbert_ref.so")),
+                    reason="oracle/_ref (the compiled reference) is not on this box")
+def test_host_tokenizer_fuzz_100k_against_compiled_reference(pkg):
+    """10^5 fuzzed UTF-8 strings through bert_tokenize of the COMPILED reference (bert.cpp:297-417 as
+    built by oracle/Makefile) and through the product's host tokenizer; ids must be identical.  English and Chinese
+    vocabularies; strings stay short enough that the reference does not overrun its buffer (bert.cpp:408-415)."""
+    import random
+    from oracle import reflib
+    total = 0
+    for shape, seed in (("all-MiniLM-L6-v2", 11), ("bge-small-zh-v1.5", 12)):
+        model = synth.model_path(shape, "q4_0" if "Mini" in shape else "q4_1")
+        vocab = synth.make_vocab(synth.SHAPES[shape][4], 0)
+        ref = reflib.RefBert(model)
+        m = pkg.BertModel(model, host_only=True)
+        rnd = random.Random(seed)
+        words = [w for w in vocab[104:] if 0 < len(w) < 12]
+        pieces = [b" ", b" ", b" ", b"!", b"#", b"##", b".", b",", b"?", b"\t", b"\n", b"A", b"Zq", b"\xc3\x89", b"\xc3\xa9", b"\xc3",
+                  b"\x80", b"\xff", b"\xe4\xbd", b"\xf0\x9f\x98\x80", "你".encode(), "好，".encode(), "こ".encode(), "！".encode(),
+                  "（".encode(), b"123", b"dup", b"##dup", b"[CLS]", b"[unused5]"]
+        texts = []
+        for _ in range(50000):
+            k = rnd.randint(0, 14)
+            texts.append(b"".join(rnd.choice(words) if rnd.random() < 0.5 else rnd.choice(pieces) for _ in range(k)).replace(b"\0", b" "))
+        ids, lens = m.tokenize_batch(texts)
+        off = 0
+        for t, n in zip(texts, lens.tolist()):
+            want = ref.tokenize(t)
+            assert ids[off:off + n].tolist() == want, (shape, t)
+            off += n
+        total += len(texts)
+        m.close()
+        ref.close()
+    assert total == 100000
+
+
 def test_loader_error_conventions(pkg, tmp_path, capfd):
     L = pkg.lib()
     assert not L.bertx_load_host_only(str(tmp_path / "missing.bin").encode())
@@ -121,32 +156,83 @@ def test_product_never_touches_the_oracle():
 WORKER = r'''
 import os, sys, json
 sys.path.insert(0, %(root)r)
+import numpy as np
 import torch, torch.distributed as dist
 import bench
+import __graft_entry__ as ge
 dist.init_process_group("gloo")
 rank, world = dist.get_rank(), dist.get_world_size()
-n = 37
-lo, hi = bench.shard_range(n, rank, world)
-# every rank "encodes" its shard (a deterministic stand-in) and the shards tile the job exactly
-mine = torch.zeros(n, dtype=torch.float64)
-mine[lo:hi] = torch.arange(lo, hi, dtype=torch.float64) * 3 + 1
-dist.all_reduce(mine)
-assert torch.equal(mine, torch.arange(n, dtype=torch.float64) * 3 + 1)
+# the N > 1 path of bench.py on CPU: the global batch is generated once from one seed, every rank takes its
+# shard_range() slice, tokenises it with the product's host tokenizer and cuts it into micro-batches (bertx_plan on a
+# host-only context); the shards must tile the batch exactly and every sentence must land in exactly one micro-batch
+pkg = ge.load_package()
+shape, kind, total = "tiny-d64", "client", 1201
+texts = bench.make_texts(shape, kind, total, 0)
+lo, hi = bench.shard_range(total, rank, world)
+m = pkg.BertModel(bench.model_file(shape, "q4_0"), host_only=True)
+ids, lens = m.tokenize_batch(texts[lo:hi])
+mb_of, mb_tok = m.plan(lens, n_devices=1)
+assert len(mb_of) == hi - lo and mb_of.min() == 0 and mb_of.max() == len(mb_tok) - 1
+assert np.array_equal(np.bincount(mb_of, weights=lens, minlength=len(mb_tok)).astype(np.int64), mb_tok.astype(np.int64))
+cover = torch.zeros(total, dtype=torch.float64)
+cover[lo:hi] = 1.0
+tok = torch.tensor([float(lens.sum()), float(hi - lo), float(len(mb_tok))], dtype=torch.float64)
+dist.all_reduce(cover)
+dist.all_reduce(tok)
+assert torch.equal(cover, torch.ones(total, dtype=torch.float64))          # the shards tile the job exactly
+_, all_lens = m.tokenize_batch(texts)
+assert tok[0].item() == float(all_lens.sum()) and tok[1].item() == total
 t = torch.tensor([float(rank + 1)])
 dist.all_reduce(t, op=dist.ReduceOp.MAX)          # the bench's max-over-ranks timing rule
 assert t.item() == world
-if rank == 0: print("OK", lo, hi)
+if rank == 0: print("OK", lo, hi, int(tok[2].item()))
+m.close()
 dist.destroy_process_group()
 '''
 
 
 def test_sentence_sharding_world_size_2_gloo(tmp_path):
+    synth.model_path("tiny-d64", "q4_0")                  # generate once, before two ranks race on the cache
     script = tmp_path / "w.py"
     script.write_text(WORKER % {"root": ROOT})
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
                         "--master-addr", "127.0.0.1", "--master-port", "29571", str(script)],
                        capture_output=True, text=True, timeout=300)
-    assert r.returncode == 0 and "OK 0 19" in r.stdout, r.stdout + r.stderr
+    assert r.returncode == 0 and "OK 0 601" in r.stdout, r.stdout + r.stderr
+
+
+def test_micro_batch_planner_properties(pkg, monkeypatch):
+    """The scheduler behind bert_encode_batch (csrc/pipeline.cu; reference bert.cpp:1394-1443 re-designed) on token counts
+    alone, through a host-only context: deterministic chunks on 16-sentence boundaries with a ramp (small first chunks
+    start the GPUs early), sentences sorted by length inside a chunk, micro-batches packed to the token budget and
+    split over the GPUs."""
+    monkeypatch.setenv("BERT_MICROBATCH_TOKENS", "8192")
+    m = pkg.BertModel(synth.model_path("tiny-d64", "q4_0"), host_only=True)
+    rng = np.random.default_rng(3)
+    for n, nd in ((5, 1), (16, 2), (17, 1), (1000, 1), (5000, 1), (5000, 2), (5000, 8), (40000, 8)):
+        lens = rng.integers(2, 513, n).astype(np.int32)
+        mb_of, mb_tok = m.plan(lens, n_devices=nd)
+        mb_of2, mb_tok2 = m.plan(lens, n_devices=nd)
+        assert np.array_equal(mb_of, mb_of2) and np.array_equal(mb_tok, mb_tok2)        # a function of the counts only
+        assert np.array_equal(np.bincount(mb_of, weights=lens, minlength=len(mb_tok)).astype(np.int64), mb_tok)
+        assert mb_tok.max() <= 8192 and mb_tok.min() >= 2                               # token budget respected
+        first = np.array([np.nonzero(mb_of == k)[0].min() for k in range(len(mb_tok))])
+        last = np.array([np.nonzero(mb_of == k)[0].max() for k in range(len(mb_tok))])
+        # micro-batches of a chunk interleave inside it, chunks do not: chunk starts are multiples of 16 sentences
+        pmax = np.maximum.accumulate(last)
+        smin = np.minimum.accumulate(first[::-1])[::-1]
+        chunk_start = [0] + [int(smin[k]) for k in range(1, len(mb_tok)) if pmax[k - 1] < smin[k]]
+        assert all(c % 16 == 0 for c in chunk_start)
+        if n >= 5000:
+            # inside a chunk a micro-batch never holds a shorter sentence than a later micro-batch's longest
+            k0 = [k for k in range(len(mb_tok)) if first[k] >= chunk_start[1] and (len(chunk_start) < 3 or last[k] < chunk_start[2])]
+            for a, b in zip(k0[:-1], k0[1:]):
+                assert lens[mb_of == a].min() >= lens[mb_of == b].max()
+        if nd > 1 and n >= 5000:
+            # a chunk is split over the GPUs: at least nd micro-batches share every full chunk
+            sizes = np.diff(chunk_start + [n])
+            assert len(mb_tok) >= nd * (len(sizes) - 1)
+    m.close()
 
 
 def test_shard_range_properties():

@@ -65,7 +65,7 @@ def make_vocab(n_vocab, seed=0):
     return v[:n_vocab]
 
 
-def make_weights(H, I, n_layer, n_vocab, n_max_tokens=512, seed=0):
+def make_weights(H, I, n_layer, n_vocab, n_max_tokens=512, seed=0, outliers=False):
     """Random weights with BERT-like statistics: unit-variance attention logits (Q/K sigma
     1/sqrt(H)) and sub-layer outputs at about half the residual stream's scale (O and FFN-out
     sigma 0.5/sqrt(fan_in)), LayerNorm gamma near 1.  Sharper/larger choices make a 12-layer
@@ -108,23 +108,36 @@ def make_weights(H, I, n_layer, n_vocab, n_max_tokens=512, seed=0):
         t[p + "output.dense.bias"] = vec(H, 0.05)
         t[p + "output.LayerNorm.weight"] = vec(H, 0.1, 1.0)
         t[p + "output.LayerNorm.bias"] = vec(H, 0.05)
+    if outliers:
+        # Outlier-stress variant: real BERT / BGE checkpoints carry a handful of hidden channels whose LayerNorm gain and
+        # dense biases are 20-50x the typical magnitude, so the residual stream has a few huge coordinates (the
+        # real-weight caveat of 8c).  Four fixed channels get that treatment in every LayerNorm and every output bias.
+        orng = np.random.default_rng(9000 + seed)
+        ch = orng.choice(H, 4, replace=False)
+        for name, w in t.items():
+            if name.endswith("LayerNorm.weight"):
+                w[ch] = orng.uniform(20.0, 50.0, 4).astype(np.float32) * orng.choice([-1.0, 1.0], 4).astype(np.float32)
+            elif name.endswith("LayerNorm.bias"):
+                w[ch] = orng.uniform(1.0, 2.5, 4).astype(np.float32) * orng.choice([-1.0, 1.0], 4).astype(np.float32)
+            elif name.endswith("output.dense.bias"):
+                w[ch] = orng.uniform(1.0, 2.5, 4).astype(np.float32) * orng.choice([-1.0, 1.0], 4).astype(np.float32)
     return t
 
 
-def model_path(shape, ftype, seed=0, n_layer=None, n_max_tokens=512):
+def model_path(shape, ftype, seed=0, n_layer=None, n_max_tokens=512, outliers=False):
     """Return the path of the (cached) synthetic model file, generating it if needed."""
     H, I, nh, nl, nv = SHAPES[shape]
     if n_layer is not None:
         nl = n_layer
     ft = fileformat.FTYPE_IDS[ftype] if isinstance(ftype, str) else ftype
     os.makedirs(CACHE, exist_ok=True)
-    tag = f"{shape}-L{nl}-P{n_max_tokens}-s{seed}-v2-{fileformat.FTYPE_NAMES[ft]}"
+    tag = f"{shape}-L{nl}-P{n_max_tokens}-s{seed}-v2{'-outl' if outliers else ''}-{fileformat.FTYPE_NAMES[ft]}"
     path = os.path.join(CACHE, f"ggml-model-{tag}.bin")
     if os.path.exists(path):
         return path
     hp = fileformat.Hparams(nv, n_max_tokens, H, I, nh, nl, ft)
     vocab = make_vocab(nv, seed)
-    w = make_weights(H, I, nl, nv, n_max_tokens, seed)
+    w = make_weights(H, I, nl, nv, n_max_tokens, seed, outliers)
     tmp = path + f".tmp{os.getpid()}"
     fileformat.write_model(tmp, hp, vocab, w, ft)
     os.replace(tmp, path)
