@@ -172,6 +172,12 @@ struct Engine {
     bool slot_submit(Replica & r, int s, MbTask & t, bool notify);
     void slot_retire(Replica & r, int s, MbTask & t, bool ok);
 
+    // BERT_TRACE=1: timestamped host-side events of each bert_encode_batch call, printed to stderr when the call returns
+    bool tracing = false;
+    std::mutex trace_mu;
+    std::vector<std::pair<double, std::string>> trace_ev;
+    void trace(const char * what, long a = 0, long b = 0);
+
     std::vector<std::thread> workers;
     std::mutex q_mu;
     std::condition_variable q_cv;

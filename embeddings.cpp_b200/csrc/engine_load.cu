@@ -202,6 +202,7 @@ bool Engine::init_devices(const ModelFile & mf) {
     fq_type = (hp.ftype == W_Q4_0 || hp.ftype == W_Q4_1) ? hp.ftype : -1;
     if (const char * e = getenv("BERT_ACT_QUANT")) { if (atoi(e) == 0) fq_type = -1; }
     init_limits();
+    if (const char * e = getenv("BERT_TRACE")) tracing = atoi(e) != 0;
     if (const char * e = getenv("BERT_POOLING")) pooling = strcmp(e, "cls") == 0 ? 1 : 0;
     if (const char * e = getenv("BERT_SMALL_T")) small_t = atoi(e);
     if (const char * e = getenv("BERT_GELU_H2")) gelu_h2 = atoi(e) != 0;

@@ -5,7 +5,9 @@
 // k-1 overlap the forward of k.  Nothing here depends on timing: which sentences share a micro-batch is a function
 // of the token counts only, so results are bit-identical from run to run and for any number of host threads.
 #include <algorithm>
+#include <chrono>
 #include <new>
+#include <string>
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
@@ -14,6 +16,18 @@
 #include "engine.h"
 
 namespace b200 {
+
+static double now_us() {
+    return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+void Engine::trace(const char * what, long a, long b) {
+    if (!tracing) return;
+    char buf[160];
+    snprintf(buf, sizeof(buf), "%s %ld %ld", what, a, b);
+    std::lock_guard<std::mutex> g(trace_mu);
+    trace_ev.emplace_back(now_us(), buf);
+}
 
 // ------------------------------------------------------------------------------------ HostPool
 HostPool::~HostPool() {
@@ -107,6 +121,7 @@ void CUDART_CB slot_done_cb(void * p) {
 }  // namespace
 
 bool Engine::slot_submit(Replica & r, int s, MbTask & t, bool notify) {
+    trace("submit_begin dev/slot", r.device, s);
     int32_t * ids = r.h_ids[s];
     int32_t * cu = r.h_cu[s];
     const int n = (int) t.tok.size();
@@ -132,10 +147,12 @@ bool Engine::slot_submit(Replica & r, int s, MbTask & t, bool notify) {
         SlotCb * cb = new (r.cb_store[s]) SlotCb{this, &r, s};
         ok = cuda_ok(cudaLaunchHostFunc(r.copy_out, slot_done_cb, cb), "host callback");
     }
+    trace("submit_end tokens/sentences", t.tokens, (long) t.tok.size());
     return ok;
 }
 
 void Engine::slot_retire(Replica & r, int s, MbTask & t, bool ok) {
+    trace("retire_begin dev/slot", r.device, s);
     if (ok) ok = cuda_ok(cudaEventSynchronize(r.slot_done[s]), "slot sync");
     if (!ok) {                                                 // leave this micro-batch's outputs untouched; drain the GPU
         cudaStreamSynchronize(r.copy_in); cudaStreamSynchronize(r.stream); cudaStreamSynchronize(r.copy_out);
@@ -154,6 +171,7 @@ void Engine::slot_retire(Replica & r, int s, MbTask & t, bool ok) {
     JobState * job = t.job;
     const int tokens = t.tokens;
     t = MbTask();                                              // drops the token storage
+    trace("retire_end tokens", tokens);
     {
         std::lock_guard<std::mutex> g(job->m);
         job->pending -= 1;
@@ -163,14 +181,28 @@ void Engine::slot_retire(Replica & r, int s, MbTask & t, bool ok) {
     job->cv.notify_all();
 }
 
+// Latency path: one micro-batch on the calling thread, everything on the compute stream (no events, no hand-offs).
 bool Engine::run_inline(Replica & r, MbTask & t) {
     if (!cuda_ok(cudaSetDevice(r.device), "cudaSetDevice")) return false;
-    JobState job;
-    job.pending = 1;
-    t.job = &job;
-    const bool ok = slot_submit(r, 0, t, false);
-    slot_retire(r, 0, t, ok);
-    return job.ok;
+    int32_t * ids = r.h_ids[0];
+    int32_t * cu = r.h_cu[0];
+    const int n = (int) t.tok.size();
+    int off = 0;
+    for (int i = 0; i < n; ++i) {
+        cu[i] = off;
+        memcpy(ids + off, t.tok[i], (size_t) t.len[i] * sizeof(int32_t));
+        off += t.len[i];
+    }
+    cu[n] = off;
+    const size_t H = (size_t) hp.n_embd;
+    bool ok = cuda_ok(cudaMemcpyAsync(r.d_ids[0], ids, (size_t) off * 4, cudaMemcpyHostToDevice, r.stream), "H2D ids");
+    ok = ok && cuda_ok(cudaMemcpyAsync(r.d_cu[0], cu, (size_t) (n + 1) * 4, cudaMemcpyHostToDevice, r.stream), "H2D cu");
+    ok = ok && forward(r, r.d_ids[0], r.d_cu[0], n, off, t.max_len, r.d_out[0]);
+    ok = ok && cuda_ok(cudaMemcpyAsync(r.h_out[0], r.d_out[0], (size_t) n * H * 4, cudaMemcpyDeviceToHost, r.stream), "D2H out");
+    ok = cuda_ok(cudaStreamSynchronize(r.stream), "stream sync") && ok;
+    if (!ok) { cudaGetLastError(); return false; }
+    for (int i = 0; i < n; ++i) memcpy(t.out[i], r.h_out[0] + (size_t) i * H, H * sizeof(float));
+    return true;
 }
 
 // ------------------------------------------------------------------------------------ per-GPU worker threads
@@ -343,6 +375,8 @@ bool Engine::encode_texts(int n_threads, int n, const char ** texts, float ** ou
         fprintf(stderr, "libbert(b200): this context has no GPU replica (host-only load); there is no CPU path\n");
         return false;
     }
+    if (tracing) { std::lock_guard<std::mutex> g(trace_mu); trace_ev.clear(); }
+    trace("encode_begin sentences", n);
     const int nblocks = (n + kBlock - 1) / kBlock;
     int nt = n_threads > 0 ? n_threads : 1;
     const int hw = (int) std::thread::hardware_concurrency();
@@ -359,6 +393,7 @@ bool Engine::encode_texts(int n_threads, int n, const char ** texts, float ** ou
     int64_t produced = 0;                                      // guarded by job.m
     bool abort = false;                                        // guarded by job.m
 
+    trace("pool_run threads", nt);
     pool.run(nt, [&](int) {
         std::vector<int32_t> scratch((size_t) kBlock * N);
         int32_t lens[kBlock];
@@ -446,10 +481,18 @@ bool Engine::encode_texts(int n_threads, int n, const char ** texts, float ** ou
         std::iota(order.begin(), order.end(), 0);
         std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return lens[a] > lens[b]; });
         cut_tasks(order, ptrs.data(), lens.data(), outs.data(), piece_budget(chunk_tokens, nd), store, &job, tasks);
+        trace("chunk_ready tokens/microbatches", (long) chunk_tokens, (long) tasks.size());
         submit(tasks, job);
         ++chunk_no;
     }
     wait_job(job);
+    trace("encode_end");
+    if (tracing) {
+        std::lock_guard<std::mutex> g(trace_mu);
+        std::sort(trace_ev.begin(), trace_ev.end());
+        const double t0 = trace_ev.empty() ? 0.0 : trace_ev.front().first;
+        for (auto & ev : trace_ev) fprintf(stderr, "[bert trace] %9.1f us  %s\n", ev.first - t0, ev.second.c_str());
+    }
     return job.ok;
 }
 
