@@ -313,13 +313,18 @@ int32_t bertx_selftest_attention(int32_t n_sent, int32_t max_len, int32_t n_head
     cudaMemcpy(qkv.p, hq.data(), hq.size() * 2, cudaMemcpyHostToDevice);
     cudaMemcpy(dcu.p, cu.data(), cu.size() * 4, cudaMemcpyHostToDevice);
     cudaMemset(o1.p, 0xFF, T * H * 2);
-    if (d_head == 64 && !(seed & 2048)) {                          // production path for head size 64: tcgen05
+    {
+        // production path: the round-2 tcgen05 kernel for both head sizes; seed bit 11 selects the round-1 kernels
+        // (tcgen05 v1 for head size 64, mma.sync for 32) for A/B runs
         CUtensorMap tq, tkv;
         cudaDeviceProp prop; cudaGetDeviceProperties(&prop, 0);
         if (!make_attention_tmaps(&tq, &tkv, qkv.as<__half>(), T, H)) return -4;
-        if (!cuda_ok(launch_attention_tc(&tq, &tkv, dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1,
-                                         prop.multiProcessorCount, 0), "selftest attention_tc launch")) return -6;
-    } else if (!cuda_ok(launch_attention(qkv.as<__half>(), dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, 0), "selftest attention launch")) return -6;
+        cudaError_t ae;
+        if (!(seed & 2048)) ae = launch_attention_tc2(&tq, &tkv, dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0);
+        else if (d_head == 64) ae = launch_attention_tc(&tq, &tkv, dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0);
+        else ae = launch_attention(qkv.as<__half>(), dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, 0);
+        if (!cuda_ok(ae, "selftest attention launch")) return -6;
+    }
     if (!cuda_ok(cudaDeviceSynchronize(), "selftest attention")) return -6;
     if (!cuda_ok(launch_attention_ref(qkv.as<__half>(), dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o2.as<__half>(), -1, 0), "selftest attention_ref launch")) return -7;
     if (!cuda_ok(cudaDeviceSynchronize(), "selftest attention_ref")) return -7;
@@ -349,8 +354,10 @@ int32_t bertx_bench_attention(int32_t n_sent, int32_t len, int32_t n_head, int32
     }
     cudaMemcpy(dcu.p, cu.data(), cu.size() * 4, cudaMemcpyHostToDevice);
     CUtensorMap tq, tkv;
-    if (d_head == 64 && !make_attention_tmaps(&tq, &tkv, qkv.as<__half>(), T, H)) return -4;
+    if (!make_attention_tmaps(&tq, &tkv, qkv.as<__half>(), T, H)) return -4;
+    static const int impl = [] { const char * e = getenv("BERT_ATTN_IMPL"); return e && strcmp(e, "tc1") == 0 ? 1 : 0; }();
     auto launch = [&]() {
+        if (impl == 0) return launch_attention_tc2(&tq, &tkv, dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, prop.multiProcessorCount, 0);
         return d_head == 64
             ? launch_attention_tc(&tq, &tkv, dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, prop.multiProcessorCount, 0)
             : launch_attention(qkv.as<__half>(), dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, 0);

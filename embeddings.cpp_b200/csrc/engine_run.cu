@@ -78,6 +78,7 @@ bool Engine::forward(Replica & r, const int32_t * d_ids, const int32_t * d_cu, i
             const int dh = H / hp.n_head;
             cudaError_t ae;
             if (attn_ref) ae = launch_attention_ref(r.qkv, d_cu, n_sent, max_len, hp.n_head, dh, r.ctx, fq_type, st);
+            else if (!attn_mma && (attn_v2 || (dh == 32 && !attn_v1))) ae = launch_attention_tc2(&r.ta_q, &r.ta_kv, d_cu, n_sent, max_len, hp.n_head, dh, r.ctx, fq_type, r.num_sms, st);
             else if (dh == 64 && !attn_mma) ae = launch_attention_tc(&r.ta_q, &r.ta_kv, d_cu, n_sent, max_len, hp.n_head, dh, r.ctx, fq_type, r.num_sms, st);
             else ae = launch_attention(r.qkv, d_cu, n_sent, max_len, hp.n_head, dh, r.ctx, fq_type, st);
             L(KK_ATTN, ae, "attention");

@@ -93,6 +93,10 @@ bool make_attention_tmaps(CUtensorMap * tm_q, CUtensorMap * tm_kv, const __half 
 cudaError_t launch_attention_tc(const CUtensorMap * tm_q, const CUtensorMap * tm_kv, const int32_t * cu_seqlens,
                                 int n_sent, int max_len, int n_head, int d_head, __half * out, int fq_type,
                                 int num_sms, cudaStream_t st);
+// round-2 kernel (attention_tc2.cu): head sizes 64 and 32 (two heads per work item), eight softmax warps per CTA; same maps
+cudaError_t launch_attention_tc2(const CUtensorMap * tm_q, const CUtensorMap * tm_kv, const int32_t * cu_seqlens,
+                                 int n_sent, int max_len, int n_head, int d_head, __half * out, int fq_type,
+                                 int num_sms, cudaStream_t st);
 cudaError_t launch_attention_ref(const __half * qkv, const int32_t * cu_seqlens, int n_sent, int max_len,
                                  int n_head, int d_head, __half * out, int fq_type, cudaStream_t st);
 
