@@ -217,6 +217,7 @@ def main():
     if world > 1:
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        park = dist.new_group(backend="gloo")                   # host-side wait for the in-process leg (see below)
 
     def barrier():
         if world > 1:
@@ -368,6 +369,8 @@ def main():
     m.close()
 
     # ---- the product's own multi-GPU mode: ONE bert_encode_batch call over all N GPUs of this process (rank 0 only)
+    # The other ranks wait on a gloo (host) group: a rank parked in an NCCL barrier keeps a spinning kernel on its GPU,
+    # which rank 0's replica on that GPU would have to share the SMs with.
     if world > 1 and not args.no_inprocess:
         barrier()
         if rank == 0:
@@ -385,7 +388,7 @@ def main():
                                      "finite": bool(np.isfinite(outN).all()),
                                      "ratio_to_torchrun_e2e": (total * args.steps / dtN) / e2e_value}
             mN.close()
-        barrier()
+        dist.barrier(group=park)
     if rank == 0:
         print(json.dumps(line))
     if world > 1:

@@ -160,6 +160,7 @@ struct Engine {
     // bert_encode_batch call (small first chunks start the GPUs early); both functions of the counts only
     int piece_budget(int64_t tokens, int64_t nd) const;
     int64_t chunk_target(int chunk_no, int64_t nd) const;
+    bool chunk_complete(int64_t chunk_tokens, int64_t target, int64_t seen_tokens, int64_t seen_sent, int64_t total_sent) const;
     static constexpr int kTokBlock = 16;          // sentences per tokenizer work item; chunks end on block boundaries
     // the micro-batches bert_encode_batch would cut for these token counts on nd GPUs (host only; bertx_plan)
     int plan_encode(const int32_t * n_tokens, int n, int nd, int32_t * mb_of_sentence, std::vector<int> & mb_tokens) const;

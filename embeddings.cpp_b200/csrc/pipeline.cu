@@ -76,7 +76,16 @@ void HostPool::wait() {
 
 // ------------------------------------------------------------------------------------ micro-batches
 int64_t Engine::chunk_target(int chunk_no, int64_t nd) const {
-    return nd * std::min<int64_t>(t_cap, (int64_t) 16384 << std::min(chunk_no, 12));
+    return nd * std::min<int64_t>(t_cap, (int64_t) 32768 << std::min(chunk_no, 12));
+}
+
+// A chunk ends once it holds `target` tokens -- unless what is left of the job (estimated from the mean sentence length
+// seen so far: a function of the token counts only) is less than half a chunk, in which case the tail rides along
+// instead of becoming a small micro-batch of its own at the end of the call.
+bool Engine::chunk_complete(int64_t chunk_tokens, int64_t target, int64_t seen_tokens, int64_t seen_sent, int64_t total_sent) const {
+    if (chunk_tokens < target) return false;
+    const int64_t rest = seen_sent > 0 ? seen_tokens * (total_sent - seen_sent) / seen_sent : 0;
+    return rest >= target / 2;
 }
 
 int Engine::piece_budget(int64_t tokens, int64_t nd) const {
@@ -321,6 +330,7 @@ int Engine::plan_encode(const int32_t * n_tokens, int n, int nd, int32_t * mb_of
     std::vector<const int32_t *> tok;
     std::vector<float *> out;
     int pos = 0, chunk_no = 0;
+    int64_t seen_tokens = 0;
     const int first_kept = n <= kTokBlock ? n : 0;             // latency path: one group, run_tokens' budget
     while (pos < n) {
         const int64_t target = first_kept ? INT64_MAX : chunk_target(chunk_no, nd);
@@ -328,8 +338,8 @@ int Engine::plan_encode(const int32_t * n_tokens, int n, int nd, int32_t * mb_of
         const int first = pos;
         while (pos < n) {
             const int hi = std::min(pos + kTokBlock, n);
-            for (; pos < hi; ++pos) chunk_tokens += n_tokens[pos];
-            if (chunk_tokens >= target) break;
+            for (; pos < hi; ++pos) { chunk_tokens += n_tokens[pos]; seen_tokens += n_tokens[pos]; }
+            if (chunk_complete(chunk_tokens, target, seen_tokens, pos, n)) break;
         }
         const int cnt = pos - first;
         order.resize(cnt);
@@ -449,6 +459,7 @@ bool Engine::encode_texts(int n_threads, int n, const char ** texts, float ** ou
     std::vector<float *> outs;
     std::vector<int> order;
     int pos = 0, chunk_no = 0;
+    int64_t seen_tokens = 0;
     while (pos < nblocks) {
         // deterministic ramp: small first chunks start the GPUs early, then full token-budget chunks
         const int64_t target = chunk_target(chunk_no, nd);
@@ -464,9 +475,10 @@ bool Engine::encode_texts(int n_threads, int n, const char ** texts, float ** ou
             }
             job.cv.notify_all();
             chunk_tokens += (int64_t) blocks[pos].ids.size();
+            seen_tokens += (int64_t) blocks[pos].ids.size();
             store->blocks.push_back(std::move(blocks[pos]));
             ++pos;
-            if (chunk_tokens >= target) break;
+            if (chunk_complete(chunk_tokens, target, seen_tokens, std::min<int64_t>((int64_t) pos * kBlock, n), n)) break;
         }
         ptrs.clear(); lens.clear(); outs.clear();
         int sent = first_block * kBlock;
