@@ -93,6 +93,8 @@ def lib():
     L.bertx_selftest_attention.argtypes = [c_i32, c_i32, c_i32, c_i32, c_i32, pf, pf]
     L.bertx_quantize_file.restype = c_i32
     L.bertx_quantize_file.argtypes = [cp, cp, c_i32]
+    L.bertx_quantize_rows_noalloc.restype = c_i32
+    L.bertx_quantize_rows_noalloc.argtypes = [vp, c_i32, c_i64, c_i32, vp]
     _lib = L
     return L
 
@@ -244,6 +246,19 @@ def quantize_file(fname_inp, fname_out, itype):
     rc = lib().bertx_quantize_file(os.fsencode(fname_inp), os.fsencode(fname_out), itype)
     if rc != 0:
         raise RuntimeError(f"bertx_quantize_file failed ({rc}, see stderr)")
+
+
+def quantize_rows_noalloc(values, itype):
+    """q4_0 (itype 2) / q4_1 (itype 3) blocks of a float32 or float16 array through bertx_quantize_rows_noalloc (fixed
+    device scratch, no allocation; at most 1 Mi values per call).  Returns the block bytes as a uint8 array."""
+    a = np.ascontiguousarray(values)
+    if a.dtype not in (np.float32, np.float16):
+        raise TypeError("float32 or float16 values")
+    out = np.empty(max(a.size // 32, 1) * (18 if itype == 2 else 20), dtype=np.uint8)
+    rc = lib().bertx_quantize_rows_noalloc(a.ctypes.data, 0 if a.dtype == np.float32 else 1, a.size, itype, out.ctypes.data)
+    if rc != 0:
+        raise RuntimeError(f"bertx_quantize_rows_noalloc failed ({rc}, see stderr)")
+    return out[:a.size // 32 * (18 if itype == 2 else 20)]
 
 
 def selftest_gemm(M, N, K, wtype, epilogue, seed=0):

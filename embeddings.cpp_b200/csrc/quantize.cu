@@ -15,6 +15,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -188,4 +189,97 @@ extern "C" int32_t bertx_quantize_file(const char * fname_inp, const char * fnam
         fflush(stdout);
     }
     return rc;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// bertx_quantize_rows_noalloc: the same block quantiser for callers that cannot allocate device memory (no counterpart
+// in the reference).  The device copies of the source values and of the
+// q4 blocks -- what bertx_quantize_file above holds in cudaMalloc'ed buffers -- live in ONE file-scope __device__ array
+// of a fixed size, which every GPU that loads this module keeps until the process exits.
+//
+// Rules that follow from that:
+//   * in host code `g_noalloc_scratch` is only a handle for the symbol, not a device address; the address is fetched once
+//     per device with cudaGetSymbolAddress (that device current) and that pointer is what the kernel receives;
+//   * every call uses the same array and finds the previous call's bytes in it.  Nothing has to start at zero here: the
+//     kernel writes every byte of the output region that is copied back, and reads only source bytes this call uploaded;
+//   * two calls that overlap on one GPU would race on the array.  Calls of one process are serialised by a host mutex and
+//     the entry point returns only after its device work has finished, so that cannot happen through this entry point;
+//     anything else that were to borrow the array would have to queue behind it.
+namespace {
+
+constexpr size_t kNoAllocMaxElems = (size_t) 1 << 20;                    // values per call (32 768 blocks)
+constexpr size_t kNoAllocSrcBytes = kNoAllocMaxElems * 4;                // f32 source
+constexpr size_t kNoAllocDstBytes = kNoAllocMaxElems / QK * 20;          // q4_1 blocks (the larger of the two)
+constexpr size_t kNoAllocBytes = kNoAllocSrcBytes + kNoAllocDstBytes;    // 4.625 MiB per GPU
+static_assert(kNoAllocSrcBytes % 256 == 0, "the block region starts 256-byte aligned");
+
+static __device__ __align__(256) uint8_t g_noalloc_scratch[kNoAllocBytes];
+
+constexpr int kNoAllocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+uint8_t * g_noalloc_addr[kNoAllocMaxDevices] = {};                       // device address of the array, per device ordinal
+
+// Device address of the scratch array on the CURRENT device (looked up once per device).  Caller holds g_noalloc_mu.
+uint8_t * noalloc_scratch_addr(const char * fn) {
+    int dev = -1;
+    cudaError_t ce = cudaGetDevice(&dev);
+    if (ce != cudaSuccess || dev < 0 || dev >= kNoAllocMaxDevices) {
+        fprintf(stderr, "%s: no usable current CUDA device (%s)\n", fn, ce != cudaSuccess ? cudaGetErrorString(ce) : "ordinal out of range");
+        return nullptr;
+    }
+    if (!g_noalloc_addr[dev]) {
+        void * p = nullptr;
+        ce = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (ce != cudaSuccess || !p) {
+            fprintf(stderr, "%s: cudaGetSymbolAddress failed on device %d: %s\n", fn, dev, cudaGetErrorString(ce));
+            return nullptr;
+        }
+        g_noalloc_addr[dev] = (uint8_t *) p;
+    }
+    return g_noalloc_addr[dev];
+}
+
+}  // namespace
+
+extern "C" int32_t bertx_quantize_rows_noalloc(const void * src, int32_t src_ftype, int64_t n_elems, int32_t itype, void * dst) {
+    const char * fn = "bertx_quantize_rows_noalloc";
+    if (itype != 2 && itype != 3) { fprintf(stderr, "%s: invalid quantization type %d\n", fn, itype); return 1; }
+    if (src_ftype != 0 && src_ftype != 1) { fprintf(stderr, "%s: source type %d is neither f32 (0) nor f16 (1)\n", fn, src_ftype); return 6; }
+    if (!src || !dst || n_elems <= 0 || n_elems % QK != 0) {
+        fprintf(stderr, "%s: need non-null buffers and a positive multiple of %d values (got %lld)\n", fn, QK, (long long) n_elems);
+        return 6;
+    }
+    if ((uint64_t) n_elems > kNoAllocMaxElems) {
+        fprintf(stderr, "%s: %lld values exceed the fixed scratch of %zu values per call (%zu bytes per GPU); split the rows over several calls\n",
+                fn, (long long) n_elems, kNoAllocMaxElems, kNoAllocBytes);
+        return 9;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) {
+        fprintf(stderr, "%s: no CUDA device (the quantiser is a GPU kernel; there is no CPU path)\n", fn);
+        return 2;
+    }
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    uint8_t * scratch = noalloc_scratch_addr(fn);
+    if (!scratch) return 7;
+    uint8_t * d_src = scratch;
+    uint8_t * d_dst = scratch + kNoAllocSrcBytes;
+    const size_t n_blocks = (size_t) n_elems / QK, out_bytes = n_blocks * (itype == 2 ? 18 : 20);
+    const size_t in_bytes = (size_t) n_elems * (src_ftype == 0 ? 4 : 2);
+    cudaError_t ce = cudaMemcpy(d_src, src, in_bytes, cudaMemcpyHostToDevice);
+    if (ce == cudaSuccess) {
+        const int wpb = 8;
+        const unsigned grid = (unsigned) ((n_blocks + wpb - 1) / wpb);
+        if (src_ftype == 1 && itype == 2) quantize_q4_kernel<true, 2><<<grid, 32 * wpb>>>(d_src, d_dst, n_blocks);
+        else if (src_ftype == 1) quantize_q4_kernel<true, 3><<<grid, 32 * wpb>>>(d_src, d_dst, n_blocks);
+        else if (itype == 2) quantize_q4_kernel<false, 2><<<grid, 32 * wpb>>>(d_src, d_dst, n_blocks);
+        else quantize_q4_kernel<false, 3><<<grid, 32 * wpb>>>(d_src, d_dst, n_blocks);
+        ce = cudaGetLastError();
+    }
+    if (ce == cudaSuccess) ce = cudaMemcpy(dst, d_dst, out_bytes, cudaMemcpyDeviceToHost);   // also waits for the kernel
+    if (ce != cudaSuccess) {
+        fprintf(stderr, "%s: CUDA failure: %s\n", fn, cudaGetErrorString(ce));
+        return 8;
+    }
+    return 0;
 }

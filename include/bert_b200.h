@@ -99,6 +99,17 @@ BERT_API int32_t bertx_debug_gemm(int32_t M, int32_t N, int32_t K, int32_t wtype
  * quantisation runs as a CUDA kernel; returns 0 on success, non-zero (+ message on stderr) otherwise. */
 BERT_API int32_t bertx_quantize_file(const char * fname_inp, const char * fname_out, int32_t itype);
 
+/* No counterpart in the reference; added for callers that cannot allocate
+ * device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The block quantiser of
+ * bertx_quantize_file on caller-owned HOST buffers: src holds n_elems values (src_ftype 0 = f32, 1 = f16; a whole
+ * number of 32-value blocks), dst receives n_elems / 32 blocks of 18 (itype 2, q4_0) or 20 (itype 3, q4_1) bytes, the
+ * same bytes bertx_quantize_file writes for those values.  Calls no cudaMalloc / cudaFree: the device staging lives in a
+ * fixed __device__ array of 4.625 MiB that every GPU using the entry point keeps until exit.  Limit: n_elems <=
+ * 1 048 576 per call (larger inputs: split on block boundaries; return code 9 and a message otherwise).  Runs on the
+ * current device, returns after the result is in dst.  All calls share the array (calls of one process are serialised
+ * inside; work that overlapped on the GPU would race on it).  Returns 0 on success. */
+BERT_API int32_t bertx_quantize_rows_noalloc(const void * src, int32_t src_ftype, int64_t n_elems, int32_t itype, void * dst);
+
 #ifdef __cplusplus
 }
 #endif
