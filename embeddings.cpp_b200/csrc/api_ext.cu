@@ -284,6 +284,18 @@ int32_t bertx_bench_gemm(int32_t M, int32_t N, int32_t K, int32_t wtype, int32_t
     return gemm_test_impl(M, N, K, wtype, epilogue, 1, &a, &b, reps, ms_total);
 }
 
+// Attention kernel the engine picks for this head size (engine_run.cu), 0 = attention_tc.cu (head size 64), 1 = attention_tc2.cu,
+// 2 = the mma.sync validation kernel, 3 = attention_tc3.cu (head size 64); BERT_ATTN_IMPL = tc1 | tc2 | tc3 | mma overrides as
+// it does for the engine
+static int attn_impl_for(int d_head) {
+    const char * e = getenv("BERT_ATTN_IMPL");
+    if (e && strcmp(e, "mma") == 0) return 2;
+    if (e && strcmp(e, "tc2") == 0) return 1;
+    if (e && strcmp(e, "tc1") == 0) return d_head == 64 ? 0 : 2;
+    if (e && strcmp(e, "tc3") == 0) return d_head == 64 ? 3 : 1;
+    return d_head == 64 ? 0 : 1;
+}
+
 int32_t bertx_selftest_attention(int32_t n_sent, int32_t max_len, int32_t n_head, int32_t d_head, int32_t seed,
                                  float * max_abs_err, float * max_ref) {
     if (n_sent <= 0 || max_len <= 0 || (d_head != 32 && d_head != 64)) return -1;
@@ -314,14 +326,16 @@ int32_t bertx_selftest_attention(int32_t n_sent, int32_t max_len, int32_t n_head
     cudaMemcpy(dcu.p, cu.data(), cu.size() * 4, cudaMemcpyHostToDevice);
     cudaMemset(o1.p, 0xFF, T * H * 2);
     {
-        // production path: the round-2 tcgen05 kernel for both head sizes; seed bit 11 selects the round-1 kernels
-        // (tcgen05 v1 for head size 64, mma.sync for 32) for A/B runs
+        // the engine's own dispatch (attn_impl_for) unless a seed bit names a kernel: bit 11 the round-1 kernels (tcgen05 v1
+        // for head size 64, mma.sync for 32), bit 12 the eight-softmax-warp kernel, bit 13 the round-2 study kernel attention_tc3.cu (head size 64)
         CUtensorMap tq, tkv;
         cudaDeviceProp prop; cudaGetDeviceProperties(&prop, 0);
         if (!make_attention_tmaps(&tq, &tkv, qkv.as<__half>(), T, H)) return -4;
+        const int impl = (seed & 2048) ? (d_head == 64 ? 0 : 2) : (seed & 4096) ? 1 : (seed & 8192) ? (d_head == 64 ? 3 : 1) : attn_impl_for(d_head);
         cudaError_t ae;
-        if (!(seed & 2048)) ae = launch_attention_tc2(&tq, &tkv, dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0);
-        else if (d_head == 64) ae = launch_attention_tc(&tq, &tkv, dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0);
+        if (impl == 3) ae = launch_attention_tc3(&tq, &tkv, dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0);
+        else if (impl == 1) ae = launch_attention_tc2(&tq, &tkv, dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0);
+        else if (impl == 0) ae = launch_attention_tc(&tq, &tkv, dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0);
         else ae = launch_attention(qkv.as<__half>(), dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, 0);
         if (!cuda_ok(ae, "selftest attention launch")) return -6;
     }
@@ -355,12 +369,12 @@ int32_t bertx_bench_attention(int32_t n_sent, int32_t len, int32_t n_head, int32
     cudaMemcpy(dcu.p, cu.data(), cu.size() * 4, cudaMemcpyHostToDevice);
     CUtensorMap tq, tkv;
     if (!make_attention_tmaps(&tq, &tkv, qkv.as<__half>(), T, H)) return -4;
-    static const int impl = [] { const char * e = getenv("BERT_ATTN_IMPL"); return e && strcmp(e, "tc1") == 0 ? 1 : 0; }();
+    const int impl = attn_impl_for(d_head);
     auto launch = [&]() {
-        if (impl == 0) return launch_attention_tc2(&tq, &tkv, dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, prop.multiProcessorCount, 0);
-        return d_head == 64
-            ? launch_attention_tc(&tq, &tkv, dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, prop.multiProcessorCount, 0)
-            : launch_attention(qkv.as<__half>(), dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, 0);
+        if (impl == 3) return launch_attention_tc3(&tq, &tkv, dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, prop.multiProcessorCount, 0);
+        if (impl == 1) return launch_attention_tc2(&tq, &tkv, dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, prop.multiProcessorCount, 0);
+        if (impl == 0) return launch_attention_tc(&tq, &tkv, dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, prop.multiProcessorCount, 0);
+        return launch_attention(qkv.as<__half>(), dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, 0);
     };
     if (!cuda_ok(launch(), "bench attention launch") || !cuda_ok(cudaDeviceSynchronize(), "bench attention")) return -6;
     cudaEvent_t e0, e1;
@@ -373,6 +387,16 @@ int32_t bertx_bench_attention(int32_t n_sent, int32_t len, int32_t n_head, int32
     if (ok) cudaEventElapsedTime(&ms, e0, e1);
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     *ms_total = ms;
+    if (ok && impl == 3 && getenv("BERT_ATTN_PROF")) {            // wait clocks of CTA 0 (only a -DBERT_ATTN3_PROF=1 build counts)
+        unsigned long long c[32];
+        attn3_prof_fetch(c);
+        const double n = (double) (reps + 1);
+        fprintf(stderr, "attn3 prof (clocks per launch, CTA 0): MMA warp total %.0f = q_full %.0f + k_full %.0f + p_ready %.0f + o_free %.0f + v_full %.0f + rest; blocks %.0f items %.0f\n"
+                        "  softmax warp total %.0f: s_full(next) %.0f s_full(first) %.0f pv_done(final) %.0f finalize %.0f\n"
+                        "  producer total %.0f: q_empty %.0f k_empty %.0f v_empty %.0f\n",
+                c[5] / n, c[0] / n, c[1] / n, c[2] / n, c[3] / n, c[4] / n, c[6] / n, c[7] / n,
+                c[11] / n, c[8] / n, c[9] / n, c[10] / n, c[12] / n, c[19] / n, c[16] / n, c[17] / n, c[18] / n);
+    }
     return ok ? 0 : -6;
 }
 

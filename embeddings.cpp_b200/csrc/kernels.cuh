@@ -97,6 +97,11 @@ cudaError_t launch_attention_tc(const CUtensorMap * tm_q, const CUtensorMap * tm
 cudaError_t launch_attention_tc2(const CUtensorMap * tm_q, const CUtensorMap * tm_kv, const int32_t * cu_seqlens,
                                  int n_sent, int max_len, int n_head, int d_head, __half * out, int fq_type,
                                  int num_sms, cudaStream_t st);
+// round-2 kernel for head size 64 (attention_tc3.cu): three S buffers in TMEM, separate K / V rings, software-pipelined softmax
+cudaError_t launch_attention_tc3(const CUtensorMap * tm_q, const CUtensorMap * tm_kv, const int32_t * cu_seqlens,
+                                 int n_sent, int max_len, int n_head, int d_head, __half * out, int fq_type,
+                                 int num_sms, cudaStream_t st);
+void attn3_prof_fetch(unsigned long long * out);      // diagnostic counters of a -DBERT_ATTN3_PROF=1 build
 cudaError_t launch_attention_ref(const __half * qkv, const int32_t * cu_seqlens, int n_sent, int max_len,
                                  int n_head, int d_head, __half * out, int fq_type, cudaStream_t st);
 

@@ -99,6 +99,21 @@ BERT_API int32_t bertx_debug_gemm(int32_t M, int32_t N, int32_t K, int32_t wtype
  * quantisation runs as a CUDA kernel; returns 0 on success, non-zero (+ message on stderr) otherwise. */
 BERT_API int32_t bertx_quantize_file(const char * fname_inp, const char * fname_out, int32_t itype);
 
+/* Checkpoint conversion on the box: a Hugging Face BERT checkpoint (model.safetensors, tensors F32 / F16 /
+ * BF16) + config.json + vocab.txt -> fname_out in the reference's model format, byte-for-byte what
+ * `python models/convert-to-ggml.py dir ftype` writes (models/convert-to-ggml.py:68-110; ftype 0 f32, 1 f16) and, for
+ * ftype 2 (q4_0) / 3 (q4_1), what `quantize ggml-model-f16.bin out.bin ftype` then makes of the f16 file
+ * (models/run_conversions.sh, models/quantize.cpp:27-268).  ftype 0 / 1 run on the host alone; the q4 block kernel is
+ * CUDA.  Returns 0 on success, non-zero (+ message on stderr) otherwise. */
+BERT_API int32_t bertx_convert_safetensors(const char * safetensors, const char * config_json, const char * vocab_txt,
+                                           int32_t ftype, const char * fname_out);
+
+/* The same conversion straight into an engine: the file image is built in an anonymous memory file and handed to
+ * bert_load_from_file, so nothing touches the disk and the q4 blocks on the device are the ones the reference's tools
+ * would have written.  Returns NULL on failure (message on stderr).  Free with bert_free. */
+BERT_API struct bert_ctx * bertx_load_from_safetensors(const char * safetensors, const char * config_json,
+                                                       const char * vocab_txt, int32_t ftype);
+
 /* No counterpart in the reference; added for callers that cannot allocate
  * device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The block quantiser of
  * bertx_quantize_file on caller-owned HOST buffers: src holds n_elems values (src_ftype 0 = f32, 1 = f16; a whole
