@@ -95,6 +95,10 @@ def lib():
     L.bertx_quantize_file.argtypes = [cp, cp, c_i32]
     L.bertx_quantize_rows_noalloc.restype = c_i32
     L.bertx_quantize_rows_noalloc.argtypes = [vp, c_i32, c_i64, c_i32, vp]
+    L.bertx_convert_safetensors.restype = c_i32
+    L.bertx_convert_safetensors.argtypes = [cp, cp, cp, c_i32, cp]
+    L.bertx_load_from_safetensors.restype = vp
+    L.bertx_load_from_safetensors.argtypes = [cp, cp, cp, c_i32]
     _lib = L
     return L
 
@@ -120,15 +124,29 @@ def _ip(a):
 class BertModel:
     """Same surface as the reference's examples/sample_dylib.py BertModel."""
 
-    def __init__(self, fname, host_only=False, n_threads=None):
+    def __init__(self, fname, host_only=False, n_threads=None, _ctx=None):
         self.lib = lib()
-        fn = fname.encode() if isinstance(fname, str) else fname
-        self.ctx = (self.lib.bertx_load_host_only if host_only else self.lib.bert_load_from_file)(fn)
+        if _ctx is not None:
+            self.ctx = _ctx
+        else:
+            fn = fname.encode() if isinstance(fname, str) else fname
+            self.ctx = (self.lib.bertx_load_host_only if host_only else self.lib.bert_load_from_file)(fn)
         if not self.ctx:
             raise RuntimeError(f"bert_load_from_file('{fname}') failed (see stderr)")
         self.n_embd = self.lib.bert_n_embd(self.ctx)
         self.n_max_tokens = self.lib.bert_n_max_tokens(self.ctx)
         self.n_threads = n_threads or min(os.cpu_count() or 1, 32)
+
+    @classmethod
+    def from_safetensors(cls, model_dir, ftype=2, n_threads=None):
+        """Load a Hugging Face checkpoint directory (model.safetensors, config.json, vocab.txt) without an
+        intermediate model file; ftype 0 f32, 1 f16, 2 q4_0, 3 q4_1 (bertx_load_from_safetensors)."""
+        L = lib()
+        ctx = L.bertx_load_from_safetensors(*[os.fsencode(os.path.join(model_dir, f))
+                                              for f in ("model.safetensors", "config.json", "vocab.txt")], ftype)
+        if not ctx:
+            raise RuntimeError(f"bertx_load_from_safetensors('{model_dir}') failed (see stderr)")
+        return cls(model_dir, n_threads=n_threads, _ctx=ctx)
 
     def __del__(self):
         try:
@@ -239,6 +257,14 @@ class BertModel:
             raise RuntimeError(f"bertx_profile_staged failed ({rc})")
         names = ["embed_ln", "gemm", "attention", "add_ln", "pool_norm", "other"]
         return {n: (float(ms[i]), int(cnt[i])) for i, n in enumerate(names)}
+
+
+def convert_safetensors(model_dir, fname_out, ftype):
+    """HF checkpoint directory -> the reference's model file (what convert-to-ggml.py, then quantize, would write)."""
+    rc = lib().bertx_convert_safetensors(*[os.fsencode(os.path.join(model_dir, f))
+                                           for f in ("model.safetensors", "config.json", "vocab.txt")], ftype, os.fsencode(fname_out))
+    if rc != 0:
+        raise RuntimeError(f"bertx_convert_safetensors failed ({rc}, see stderr)")
 
 
 def quantize_file(fname_inp, fname_out, itype):
