@@ -121,6 +121,29 @@ def _ip(a):
     return a.ctypes.data_as(ctypes.POINTER(ctypes.c_int32))
 
 
+def _text_ptrs(sentences):
+    """const char** over the texts.  Many short texts: they are joined into ONE NUL-separated buffer and the pointer table is
+    base + offsets, computed in numpy -- `(c_char_p * n)(*texts)` converts item by item (348 us for 1738 short lines, a tenth
+    of that call).  Long texts (or few): the item-by-item table, which does not copy the bytes."""
+    n = len(sentences)
+    probe = sentences[:16]
+    if n < 256 or sum(len(s) for s in probe) > 256 * len(probe):
+        return (ctypes.c_char_p * n)(*[s if isinstance(s, bytes) else s.encode("utf-8") for s in sentences])
+    try:
+        buf = b"\0".join(sentences) + b"\0"
+        bs = sentences
+    except TypeError:                                              # some (or all) are str
+        bs = [s if isinstance(s, bytes) else s.encode("utf-8") for s in sentences]
+        buf = b"\0".join(bs) + b"\0"
+    offs = np.zeros(n, dtype=np.uint64)
+    lens = np.fromiter(map(len, bs), dtype=np.uint64, count=n)
+    np.cumsum(lens[:-1] + np.uint64(1), out=offs[1:])
+    addr = offs + np.uint64(ctypes.cast(ctypes.c_char_p(buf), ctypes.c_void_p).value)
+    p = ctypes.cast(addr.ctypes.data, ctypes.POINTER(ctypes.c_char_p))
+    p._keep = (addr, buf)                                          # table and text bytes must outlive the call
+    return p
+
+
 class BertModel:
     """Same surface as the reference's examples/sample_dylib.py BertModel."""
 
@@ -166,8 +189,7 @@ class BertModel:
         out = np.zeros((n, self.n_embd), dtype=np.float32)
         if n == 0:
             return out
-        texts = (ctypes.c_char_p * n)(*[s if isinstance(s, bytes) else s.encode("utf-8") for s in sentences])
-        self.lib.bert_encode_batch(self.ctx, self.n_threads, batch_size, n, texts, _row_ptrs(out))
+        self.lib.bert_encode_batch(self.ctx, self.n_threads, batch_size, n, _text_ptrs(sentences), _row_ptrs(out))
         return out
 
     def tokenize(self, text, n_max=None):
@@ -223,11 +245,10 @@ class BertModel:
 
     def tokenize_batch(self, sentences):
         n = len(sentences)
-        texts = (ctypes.c_char_p * n)(*[s if isinstance(s, bytes) else s.encode("utf-8") for s in sentences])
         cap = n * self.n_max_tokens
-        ids = np.zeros(cap, dtype=np.int32)
+        ids = np.empty(cap, dtype=np.int32)                    # (filled by the call; untouched pages are never mapped)
         lens = np.zeros(n, dtype=np.int32)
-        tot = self.lib.bertx_tokenize_batch(self.ctx, self.n_threads, n, texts, _ip(ids), cap, _ip(lens))
+        tot = self.lib.bertx_tokenize_batch(self.ctx, self.n_threads, n, _text_ptrs(sentences), _ip(ids), cap, _ip(lens))
         if tot < 0:
             raise RuntimeError("bertx_tokenize_batch failed")
         return ids[:tot].copy(), lens

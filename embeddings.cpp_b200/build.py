@@ -20,7 +20,7 @@ FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std
          "-Xcompiler", "-fPIC,-fvisibility=hidden,-pthread", "-I", os.path.join(HERE, "..", "include")]
 if os.environ.get("BERT_DEBUG_WAIT"):
     FLAGS.append("-DBERT_DEBUG_WAIT")
-SOURCES = ["gemm_tc.cu", "attention.cu", "attention_tc.cu", "attention_tc2.cu", "attention_tc3.cu", "rowwise.cu", "upload.cu", "engine_load.cu", "engine_run.cu", "pipeline.cu",
+SOURCES = ["gemm_tc.cu", "attention_tc.cu", "attention_tc2.cu", "attention_tc3.cu", "rowwise.cu", "upload.cu", "engine_load.cu", "engine_run.cu", "pipeline.cu",
            "api.cu", "api_ext.cu", "quantize.cu", "convert.cu", "tokenizer.cpp", "model_file.cpp"]
 
 

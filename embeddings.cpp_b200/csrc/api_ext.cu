@@ -284,16 +284,13 @@ int32_t bertx_bench_gemm(int32_t M, int32_t N, int32_t K, int32_t wtype, int32_t
     return gemm_test_impl(M, N, K, wtype, epilogue, 1, &a, &b, reps, ms_total);
 }
 
-// Attention kernel the engine picks for this head size (engine_run.cu), 0 = attention_tc.cu (head size 64), 1 = attention_tc2.cu,
-// 2 = the mma.sync validation kernel, 3 = attention_tc3.cu (head size 64); BERT_ATTN_IMPL = tc1 | tc2 | tc3 | mma overrides as
-// it does for the engine
+// Attention kernel the engine picks for this head size (engine_run.cu): 0 = attention_tc.cu (head size 64), 1 = attention_tc2.cu,
+// 3 = attention_tc3.cu (head size 64); BERT_ATTN_IMPL = tc2 | tc3 overrides as it does for the engine
 static int attn_impl_for(int d_head) {
     const char * e = getenv("BERT_ATTN_IMPL");
-    if (e && strcmp(e, "mma") == 0) return 2;
-    if (e && strcmp(e, "tc2") == 0) return 1;
-    if (e && strcmp(e, "tc1") == 0) return d_head == 64 ? 0 : 2;
-    if (e && strcmp(e, "tc3") == 0) return d_head == 64 ? 3 : 1;
-    return d_head == 64 ? 0 : 1;
+    if (d_head != 64 || (e && strcmp(e, "tc2") == 0)) return 1;
+    if (e && strcmp(e, "tc3") == 0) return 3;
+    return 0;
 }
 
 int32_t bertx_selftest_attention(int32_t n_sent, int32_t max_len, int32_t n_head, int32_t d_head, int32_t seed,
@@ -326,17 +323,16 @@ int32_t bertx_selftest_attention(int32_t n_sent, int32_t max_len, int32_t n_head
     cudaMemcpy(dcu.p, cu.data(), cu.size() * 4, cudaMemcpyHostToDevice);
     cudaMemset(o1.p, 0xFF, T * H * 2);
     {
-        // the engine's own dispatch (attn_impl_for) unless a seed bit names a kernel: bit 11 the round-1 kernels (tcgen05 v1
-        // for head size 64, mma.sync for 32), bit 12 the eight-softmax-warp kernel, bit 13 the round-2 study kernel attention_tc3.cu (head size 64)
+        // the engine's own dispatch (attn_impl_for) unless a seed bit names a kernel: bit 11 attention_tc.cu, bit 12 attention_tc2.cu
+        // (eight softmax warps), bit 13 attention_tc3.cu (the round-2 study kernel); head size 32 always runs attention_tc2.cu
         CUtensorMap tq, tkv;
         cudaDeviceProp prop; cudaGetDeviceProperties(&prop, 0);
         if (!make_attention_tmaps(&tq, &tkv, qkv.as<__half>(), T, H)) return -4;
-        const int impl = (seed & 2048) ? (d_head == 64 ? 0 : 2) : (seed & 4096) ? 1 : (seed & 8192) ? (d_head == 64 ? 3 : 1) : attn_impl_for(d_head);
+        const int impl = d_head != 64 ? 1 : (seed & 2048) ? 0 : (seed & 4096) ? 1 : (seed & 8192) ? 3 : attn_impl_for(d_head);
         cudaError_t ae;
         if (impl == 3) ae = launch_attention_tc3(&tq, &tkv, dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0);
         else if (impl == 1) ae = launch_attention_tc2(&tq, &tkv, dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0);
-        else if (impl == 0) ae = launch_attention_tc(&tq, &tkv, dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0);
-        else ae = launch_attention(qkv.as<__half>(), dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, 0);
+        else ae = launch_attention_tc(&tq, &tkv, dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0);
         if (!cuda_ok(ae, "selftest attention launch")) return -6;
     }
     if (!cuda_ok(cudaDeviceSynchronize(), "selftest attention")) return -6;
@@ -373,8 +369,7 @@ int32_t bertx_bench_attention(int32_t n_sent, int32_t len, int32_t n_head, int32
     auto launch = [&]() {
         if (impl == 3) return launch_attention_tc3(&tq, &tkv, dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, prop.multiProcessorCount, 0);
         if (impl == 1) return launch_attention_tc2(&tq, &tkv, dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, prop.multiProcessorCount, 0);
-        if (impl == 0) return launch_attention_tc(&tq, &tkv, dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, prop.multiProcessorCount, 0);
-        return launch_attention(qkv.as<__half>(), dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, 0);
+        return launch_attention_tc(&tq, &tkv, dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, prop.multiProcessorCount, 0);
     };
     if (!cuda_ok(launch(), "bench attention launch") || !cuda_ok(cudaDeviceSynchronize(), "bench attention")) return -6;
     cudaEvent_t e0, e1;

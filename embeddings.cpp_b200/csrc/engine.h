@@ -126,7 +126,7 @@ struct Engine {
     std::mutex mu;                             // a context is not re-entrant (bert.h note)
     std::atomic<int64_t> launches{0};
     int fq_type = -1;                          // W_Q4_0 / W_Q4_1 when activation fake-quant is on
-    bool gemm_simt = false, attn_ref = false, attn_mma = false, attn_v1 = false, attn_v2 = false, attn_v3 = false;
+    bool gemm_simt = false, attn_ref = false, attn_v2 = false, attn_v3 = false;
     bool fuse_ln_att = true;                   // also fuse the LayerNorm after the attention-output GEMM (BERT_FUSE_LN=1: ffn-out only)
     bool fuse_ln = true;                       // LayerNorm in the epilogue of the o / ffn-out GEMMs (BERT_FUSE_LN=0 disables)  // validation kernels forced by env (debug only)
     int t_cap = 0, b_cap = 0;

@@ -198,7 +198,7 @@ bool Engine::init_devices(const ModelFile & mf) {
 
     if (const char * e = getenv("BERT_GEMM_IMPL")) gemm_simt = strcmp(e, "simt") == 0;
     if (const char * e = getenv("BERT_FUSE_LN")) { fuse_ln = atoi(e) != 0; fuse_ln_att = atoi(e) >= 2; }
-    if (const char * e = getenv("BERT_ATTN_IMPL")) { attn_ref = strcmp(e, "ref") == 0; attn_mma = strcmp(e, "mma") == 0; attn_v1 = strcmp(e, "tc1") == 0; attn_v2 = strcmp(e, "tc2") == 0; attn_v3 = strcmp(e, "tc3") == 0; }
+    if (const char * e = getenv("BERT_ATTN_IMPL")) { attn_ref = strcmp(e, "ref") == 0; attn_v2 = strcmp(e, "tc2") == 0; attn_v3 = strcmp(e, "tc3") == 0; }
     fq_type = (hp.ftype == W_Q4_0 || hp.ftype == W_Q4_1) ? hp.ftype : -1;
     if (const char * e = getenv("BERT_ACT_QUANT")) { if (atoi(e) == 0) fq_type = -1; }
     init_limits();

@@ -77,14 +77,13 @@ bool Engine::forward(Replica & r, const int32_t * d_ids, const int32_t * d_cu, i
         {
             const int dh = H / hp.n_head;
             cudaError_t ae;
-            // default: head size 64 -> attention_tc.cu, head size 32 -> attention_tc2.cu; BERT_ATTN_IMPL = tc1 | tc2 | tc3 | mma | ref
-            // (tc3 = the round-2 study kernel, 12 % slower than tc1: profiles/r2_attention.md)
-            const bool v3 = dh == 64 && attn_v3;
+            // head size 64 -> attention_tc.cu, head size 32 -> attention_tc2.cu (two heads per work item); BERT_ATTN_IMPL = tc2
+            // (eight softmax warps, either head size) | tc3 (the round-2 study kernel for head size 64, 12 % slower:
+            // profiles/r2_attention.md) | ref (SIMT validation kernel)
             if (attn_ref) ae = launch_attention_ref(r.qkv, d_cu, n_sent, max_len, hp.n_head, dh, r.ctx, fq_type, st);
-            else if (v3) ae = launch_attention_tc3(&r.ta_q, &r.ta_kv, d_cu, n_sent, max_len, hp.n_head, dh, r.ctx, fq_type, r.num_sms, st);
-            else if (!attn_mma && (attn_v2 || (dh == 32 && !attn_v1))) ae = launch_attention_tc2(&r.ta_q, &r.ta_kv, d_cu, n_sent, max_len, hp.n_head, dh, r.ctx, fq_type, r.num_sms, st);
-            else if (dh == 64 && !attn_mma) ae = launch_attention_tc(&r.ta_q, &r.ta_kv, d_cu, n_sent, max_len, hp.n_head, dh, r.ctx, fq_type, r.num_sms, st);
-            else ae = launch_attention(r.qkv, d_cu, n_sent, max_len, hp.n_head, dh, r.ctx, fq_type, st);
+            else if (dh == 64 && attn_v3) ae = launch_attention_tc3(&r.ta_q, &r.ta_kv, d_cu, n_sent, max_len, hp.n_head, dh, r.ctx, fq_type, r.num_sms, st);
+            else if (dh == 32 || attn_v2) ae = launch_attention_tc2(&r.ta_q, &r.ta_kv, d_cu, n_sent, max_len, hp.n_head, dh, r.ctx, fq_type, r.num_sms, st);
+            else ae = launch_attention_tc(&r.ta_q, &r.ta_kv, d_cu, n_sent, max_len, hp.n_head, dh, r.ctx, fq_type, r.num_sms, st);
             L(KK_ATTN, ae, "attention");
         }
         end();

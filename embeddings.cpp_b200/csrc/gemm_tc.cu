@@ -210,6 +210,24 @@ template <bool LN> struct RegBudget {
     static_assert(128 * (96 - kRegsCtrl) + 256 * (96 - kDequant) >= 256 * (kEpilogue - 96), "setmaxnreg pool");
 };
 
+// The eight epilogue warps' wait for a finished accumulator.  A warp suspended in mbarrier.try_wait is woken by every
+// barrier event of the CTA (each TMA / bulk-copy stage that lands), re-polls and goes back to sleep: ncu counted 84 polls per
+// wait and 21 % of the QKV GEMM's executed instructions in this one loop.  BERT_EPI_WAIT_LEADER=1 lets ONE warp watch the
+// mbarrier while the other seven park on a hardware named barrier -- measured (profiles/r2_gemm_poll.md): no faster (QKV
+// 0.3564 -> 0.3576 ms, FFN-in 0.543 -> 0.558 ms, bench 9 169 -> 9 090 emb/s), the polls sit in otherwise idle issue slots and
+// the barrier couples the eight warps' start.  Off.
+#ifndef BERT_EPI_WAIT_LEADER
+#define BERT_EPI_WAIT_LEADER 0
+#endif
+__device__ __forceinline__ void wait_tfull(uint64_t * bar, uint32_t parity) {
+#if BERT_EPI_WAIT_LEADER
+    if ((threadIdx.x >> 5) == CTRL_WARPS) mbar_wait(bar, parity);
+    asm volatile("bar.sync 1, %0;" :: "n"(32 * EPI_WARPS) : "memory");
+#else
+    mbar_wait(bar, parity);
+#endif
+}
+
 // Launched with a runtime cluster dimension: 2 (one CTA pair) or, with fused LayerNorm, 2 * N / BN.
 template <int BN, int WT, bool LN, bool RES, bool EPB>
 __global__ void __launch_bounds__(gemm_threads<WT>(), 1)
@@ -411,7 +429,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             const uint32_t acc_ph = (it >> 1) & 1;
             int mb, nb; tw.get(it, mb, nb);
             const int wrow0 = mb * (2 * BM) + (int) rank * BM + q * 32;
-            mbar_wait(&tfull[acc], acc_ph);
+            wait_tfull(&tfull[acc], acc_ph);
             tc_fence_after_sync();
             uint32_t hv[NBW][32];                  // pre-LN values as fp16 pairs
 #pragma unroll
@@ -598,7 +616,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         for (int it = 0; it < my_tiles; ++it) {
             const int acc = it & 1;
             const uint32_t acc_ph = (it >> 1) & 1;
-            mbar_wait(&tfull[acc], acc_ph);
+            wait_tfull(&tfull[acc], acc_ph);
             tc_fence_after_sync();
 #pragma unroll 1
             for (int bi = 0; bi < nbw; ++bi, ++j) {

@@ -85,10 +85,9 @@ cudaError_t launch_ln(const __half * x, const float * gamma, const float * beta,
 
 // K2: per (sentence, head) softmax(Q K^T / sqrt(d)) V over the sentence's own tokens.
 // qkv [T][3H] fp16 (Q | K | V, head h at columns h*d), out [T][H] fp16.
-cudaError_t launch_attention(const __half * qkv, const int32_t * cu_seqlens, int n_sent, int max_len,
-                             int n_head, int d_head, __half * out, int fq_type, cudaStream_t st);
-// tcgen05 version (head size 64): Q / K / V tiles come by TMA from the packed qkv buffer through the
-// two maps made by make_attention_tmaps (box 64 x 128 for Q, 64 x 64 for K and V).
+// All production kernels are tcgen05 code (the round-1 mma.sync kernel for head size 32 is gone): Q / K / V tiles come by TMA
+// from the packed qkv buffer through the two maps made by make_attention_tmaps (box 64 x 128 for Q, 64 x 64 for K and V).
+// attention_tc.cu: head size 64.
 bool make_attention_tmaps(CUtensorMap * tm_q, CUtensorMap * tm_kv, const __half * qkv, uint64_t rows, int H);
 cudaError_t launch_attention_tc(const CUtensorMap * tm_q, const CUtensorMap * tm_kv, const int32_t * cu_seqlens,
                                 int n_sent, int max_len, int n_head, int d_head, __half * out, int fq_type,

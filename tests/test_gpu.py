@@ -81,10 +81,10 @@ ATTN_SHAPES = [(5, 64, 2, 64), (7, 200, 4, 64), (3, 512, 12, 64), (9, 130, 12, 3
 
 @pytest.mark.parametrize("n_sent,L,nh,d", ATTN_SHAPES)
 @pytest.mark.parametrize("flags", [0, 1024, 2048, 2048 + 1024, 4096, 4096 + 1024, 8192, 8192 + 1024],
-                         ids=["default", "default-ramp", "round1", "round1-ramp", "8warp", "8warp-ramp", "3buf", "3buf-ramp"])
+                         ids=["default", "default-ramp", "tc1", "tc1-ramp", "8warp", "8warp-ramp", "3buf", "3buf-ramp"])
 def test_fused_attention_matches_reference_kernel(pkg, n_sent, L, nh, d, flags):
     """Seed bit 10: key rows grow along the sentence, so the running max keeps leaving the 2^8 window (the rescale / redo path);
-    bit 11: the round-1 kernels (attention_tc.cu for head size 64); bit 12: attention_tc2.cu; bit 13: attention_tc3.cu; none: the
+    bit 11: attention_tc.cu (head size 64; head size 32 always runs attention_tc2.cu); bit 12: attention_tc2.cu; bit 13: attention_tc3.cu; none: the
     engine's dispatch."""
     rc, err, ref = pkg.selftest_attention(n_sent, L, nh, d, seed=(L % 1024) | flags)
     assert rc == 0

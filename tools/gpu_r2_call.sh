@@ -1,13 +1,15 @@
 #!/bin/bash
-# round 2 GPU call: converter / loader tests, accuracy harness, attention self-tests of all kernels, default bench line
+# round 2 GPU call: host-runtime changes (smaller tokenizer work items for long texts, text pointer table in numpy) and the
+# removal of the mma.sync attention kernel: tests that go through bert_encode_batch, traces, bench lines
 mkdir -p gpurun_out
-echo "== converter"; timeout 300 python -m pytest tests/test_convert.py -m gpu -x -q 2>&1 | tail -4 | cut -c1-300
-echo "== attention self-tests"; timeout 300 python -m pytest tests/test_gpu.py -m gpu -x -q -k "fused_attention" 2>&1 | tail -3 | cut -c1-300
-echo "== pair similarity test"; timeout 600 python -m pytest tests/test_pair_similarity.py -m gpu -x -q 2>&1 | tail -4 | cut -c1-300
-echo "== pair similarity harness"; rm -f gpurun_out/pair_similarity_r2.jsonl
-timeout 900 python tests/pair_similarity.py --pairs 2000 --out gpurun_out/pair_similarity_r2.jsonl 2>/dev/null | grep '^{' | cut -c1-400
-timeout 900 python tests/pair_similarity.py --shape bge-small-en-v1.5 --pairs 500 --out gpurun_out/pair_similarity_r2.jsonl 2>/dev/null | grep '^{' | cut -c1-400
-echo "== bench"; timeout 300 python bench.py --no-cpu-baseline 2>/dev/null | grep '^{' > gpurun_out/r2c_bench_default.json; python - <<'PY'
+echo "== tests"; timeout 900 python -m pytest tests/test_gpu.py tests/test_examples.py -m gpu -x -q -k "not perturbed and not gemm and not config" 2>&1 | tail -4 | cut -c1-300
+for w in bge-base-q4_0-b512-s512 minilm-q4_0-b1738-var; do
+  timeout 200 python tools/e2e_trace.py $w > gpurun_out/r2c_trace_$w.log 2>&1; echo "== $w"; grep -E "chunk_ready|encode_end|python side|device-resident" gpurun_out/r2c_trace_$w.log | head -8 | cut -c1-220
+done
+for w in bge-base-q4_0-b512-s512 minilm-q4_0-b1738-var bge-small-f16-b256-s128 bge-small-zh-q4_1-b1024-var; do
+  timeout 300 python bench.py --workload $w --no-cpu-baseline 2>/dev/null | grep '^{' > gpurun_out/r2c_bench_$w.json
+  python - <<PY
 import json
-d=json.load(open('gpurun_out/r2c_bench_default.json')); print('value', round(d['value'],1), 'e2e', round(d['e2e']['value'],1), d['roofline']['by_kernel_ms'], d['clocks'])
+d=json.load(open('gpurun_out/r2c_bench_$w.json')); print('$w', 'value', round(d['value'],1), 'e2e', round(d['e2e']['value'],1), round(d['e2e']['value']/d['value'],3), d['roofline']['by_kernel_ms'])
 PY
+done
