@@ -4,6 +4,7 @@
 #include <cstdlib>
 #include <condition_variable>
 #include <cstring>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -36,13 +37,14 @@ bool tokenize_all(Engine & e, int n_threads, int n, const char ** texts, std::ve
     const int N = e.hp.n_max_tokens;
     lens.assign(n, 0);
     offs.assign(n + 1, 0);
-    std::vector<int32_t> tmp((size_t) n * N);        // like the reference (bert.cpp:1398), upper bound
+    // like the reference (bert.cpp:1398) an upper bound of N ids per text -- but not zero-filled: pages nobody writes are never mapped
+    std::unique_ptr<int32_t[]> tmp(new int32_t[(size_t) n * N]);
     int nt = n_threads > 0 ? n_threads : 1;
     const int hw = (int) std::thread::hardware_concurrency();
     if (hw > 0 && nt > hw) nt = hw;
     if (nt > n / 64 + 1) nt = n / 64 + 1;
     auto work = [&](int lo, int hi) {
-        for (int i = lo; i < hi; ++i) lens[i] = e.tok.tokenize(texts[i], tmp.data() + (size_t) i * N, N);
+        for (int i = lo; i < hi; ++i) lens[i] = e.tok.tokenize(texts[i], tmp.get() + (size_t) i * N, N);
     };
     if (nt <= 1) {
         work(0, n);
@@ -57,7 +59,7 @@ bool tokenize_all(Engine & e, int n_threads, int n, const char ** texts, std::ve
     }
     for (int i = 0; i < n; ++i) offs[i + 1] = offs[i] + (size_t) lens[i];
     ids.resize(offs[n]);
-    for (int i = 0; i < n; ++i) memcpy(ids.data() + offs[i], tmp.data() + (size_t) i * N, (size_t) lens[i] * 4);
+    for (int i = 0; i < n; ++i) memcpy(ids.data() + offs[i], tmp.get() + (size_t) i * N, (size_t) lens[i] * 4);
     return true;
 }
 

@@ -48,11 +48,37 @@ inline bool is_chinese3(const unsigned char * p, size_t avail) {
 
 }  // namespace
 
+void VocabTable::reserve(size_t n_keys) {
+    size_t cap = 16;
+    while (cap < 2 * n_keys + 2) cap <<= 1;                          // load factor <= 0.5
+    slots_.assign(cap, Slot());
+    arena_.clear();
+    mask_ = cap - 1;
+}
+
+void VocabTable::put(std::string_view key, int32_t id) {
+    const uint64_t h = hash(key);
+    const uint32_t tag = (uint32_t) (h >> 32) | 1u;
+    for (size_t i = (size_t) h & mask_;; i = (i + 1) & mask_) {
+        Slot & s = slots_[i];
+        if (s.tag == 0) {
+            s.tag = tag; s.id = id; s.len = (uint32_t) key.size();
+            if (key.size() <= sizeof(s.key)) {
+                memcpy(s.key, key.data(), key.size());
+            } else {
+                const uint32_t off = (uint32_t) arena_.size();
+                arena_.append(key.data(), key.size());
+                memcpy(s.key, &off, 4);
+            }
+            return;
+        }
+        if (s.tag == tag && s.len == key.size() && memcmp(key_of(s), key.data(), key.size()) == 0) { s.id = id; return; }
+    }
+}
+
 void Tokenizer::build(std::vector<std::string> && vocab) {
     vocab_ = std::move(vocab);
-    token_to_id_.clear();
-    subword_to_id_.clear();
-    token_to_id_.reserve(vocab_.size() * 2);
+    token_to_id_.reserve(vocab_.size());
     subword_to_id_.reserve(vocab_.size());
     id_in_token_map_.assign(vocab_.size(), 0);
     max_tok_len_ = max_sub_len_ = 0;
@@ -60,12 +86,12 @@ void Tokenizer::build(std::vector<std::string> && vocab) {
         const std::string & w = vocab_[i];
         if (w.size() >= 2 && w[0] == '#' && w[1] == '#') {
             std::string_view sub(w.data() + 2, w.size() - 2);
-            subword_to_id_[sub] = (int32_t) i;                       // operator[] = : last wins
+            subword_to_id_.put(sub, (int32_t) i);                    // operator[] = : last wins
             if (sub.size() > max_sub_len_) max_sub_len_ = sub.size();
         }
         std::string_view key(w);
-        if (token_to_id_.find(key) == token_to_id_.end()) {          // count()==0 : first wins
-            token_to_id_.emplace(key, (int32_t) i);
+        if (token_to_id_.find(key) < 0) {                            // count()==0 : first wins
+            token_to_id_.put(key, (int32_t) i);
             id_in_token_map_[i] = 1;
             if (key.size() > max_tok_len_) max_tok_len_ = key.size();
         }
@@ -86,38 +112,55 @@ int32_t Tokenizer::tokenize(const char * text, int32_t * out, int32_t n_max) con
     const size_t len = strlen(text);
     const unsigned char * src = reinterpret_cast<const unsigned char *>(text);
 
-    // 1. stripAccents (bert.cpp:221-235): walk by utf8_len, fold the 52 mapped letters
-    std::string s;
-    s.reserve(len + 8);
-    for (size_t i = 0; i < len;) {
-        const size_t n = utf8_len(src[i]);
-        if (n == 2 && i + 1 < len) {
-            const char a = accent_fold(src[i], src[i + 1]);
-            if (a) { s.push_back(a); i += 2; continue; }
+    // The two work strings keep their capacity from call to call (no allocation per sentence) and are written through raw
+    // pointers into space sized for the worst case (no per-byte capacity checks).
+    static thread_local std::string s, t;
+    bool ascii = true;
+    for (size_t i = 0; i < len; ++i) ascii &= src[i] < 0x80;
+    s.resize(len + 8);
+    char * sd = &s[0];
+    size_t sn = 0;
+    if (ascii) {
+        // 1 + 2 for pure ASCII: nothing to fold, every byte is a character start
+        for (size_t i = 0; i < len; ++i) { const char c = text[i]; sd[i] = (c >= 'A' && c <= 'Z') ? (char) (c - 'A' + 'a') : c; }
+        sn = len;
+    } else {
+        // 1. stripAccents (bert.cpp:221-235): walk by utf8_len, fold the 52 mapped letters
+        for (size_t i = 0; i < len;) {
+            const size_t n = utf8_len(src[i]);
+            if (n == 2 && i + 1 < len) {
+                const char a = accent_fold(src[i], src[i + 1]);
+                if (a) { sd[sn++] = a; i += 2; continue; }
+            }
+            const size_t take = i + n <= len ? n : len - i;           // substr clips at the end
+            for (size_t k = 0; k < take; ++k) sd[sn + k] = text[i + k];
+            sn += take;
+            i += n;
         }
-        const size_t take = i + n <= len ? n : len - i;               // substr clips at the end
-        s.append(text + i, take);
-        i += n;
-    }
-    // 2. ASCII lower-casing at character starts only (bert.cpp:244-249)
-    for (size_t i = 0; i < s.size(); i += utf8_len((unsigned char) s[i])) {
-        const char c = s[i];
-        if (c >= 'A' && c <= 'Z') s[i] = (char) (c - 'A' + 'a');
+        // 2. ASCII lower-casing at character starts only (bert.cpp:244-249)
+        for (size_t i = 0; i < sn; i += utf8_len((unsigned char) sd[i])) {
+            const char c = sd[i];
+            if (c >= 'A' && c <= 'Z') sd[i] = (char) (c - 'A' + 'a');
+        }
     }
     // 3. isolate ASCII punctuation and 3-byte CJK with spaces, byte-wise (bert.cpp:317-339)
-    std::string t;
-    t.reserve(s.size() * 2 + 8);
-    const unsigned char * p = reinterpret_cast<const unsigned char *>(s.data());
-    for (size_t i = 0; i < s.size();) {
+    t.resize(sn * 3 + 8);                                             // a punctuation byte becomes three
+    char * td = &t[0];
+    size_t tn = 0;
+    const unsigned char * p = reinterpret_cast<const unsigned char *>(sd);
+    for (size_t i = 0; i < sn;) {
         const size_t n = utf8_len(p[i]);
         if (n == 1 && is_punct(p[i])) {
-            t.push_back(' '); t.push_back((char) p[i]); t.push_back(' ');
+            td[tn++] = ' '; td[tn++] = (char) p[i]; td[tn++] = ' ';
             i += 1;
-        } else if (n == 3 && is_chinese3(p + i, s.size() - i)) {
-            t.push_back(' '); t.append(s, i, 3); t.push_back(' ');
+        } else if (n == 3 && is_chinese3(p + i, sn - i)) {
+            const size_t take = sn - i < 3 ? sn - i : 3;              // (is_chinese3 implies all three bytes are there)
+            td[tn++] = ' ';
+            for (size_t k = 0; k < take; ++k) td[tn++] = (char) p[i + k];
+            td[tn++] = ' ';
             i += 3;
         } else {
-            t.push_back((char) p[i]);
+            td[tn++] = (char) p[i];
             i += 1;
         }
     }
@@ -125,8 +168,8 @@ int32_t Tokenizer::tokenize(const char * text, int32_t * out, int32_t n_max) con
     int32_t nt = 0;
     out[nt++] = kCls;
     if (n_max == 1) return nt;                                        // no room even for [SEP]
-    const char * tb = t.data();
-    const size_t tl = t.size();
+    const char * tb = td;
+    const size_t tl = tn;
     size_t l = 0;
     while (l < tl) {
         while (l < tl && is_space((unsigned char) tb[l])) ++l;
@@ -138,16 +181,16 @@ int32_t Tokenizer::tokenize(const char * text, int32_t * out, int32_t n_max) con
         l = r;
         const int32_t prev = nt;
         size_t i = 0;
-        const std::unordered_map<std::string_view, int32_t> * map = &token_to_id_;
+        const VocabTable * map = &token_to_id_;
         size_t maxlen = max_tok_len_;
         while (i < n) {
             if (nt >= n_max - 1) break;
             size_t j = n - i > maxlen ? i + maxlen : n;               // longer pieces cannot match
             bool found = false;
             for (; j > i; --j) {
-                auto it = map->find(std::string_view(w + i, j - i));
-                if (it != map->end()) {
-                    out[nt++] = it->second;
+                const int32_t id = map->find(std::string_view(w + i, j - i));
+                if (id >= 0) {
+                    out[nt++] = id;
                     i = j;
                     found = true;
                     break;
