@@ -214,12 +214,69 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------ MMA issuer
-        constexpr uint32_t idesc_s = umma_idesc_f16(AQ, AK);            // Q (K-major) x K (K-major)
-        constexpr uint32_t idesc_o = umma_idesc_f16(AQ, AD, 1);         // P (TMEM) x V (MN-major)
-#if BERT_ATTN_MMASUM
-        constexpr uint32_t idesc_l = umma_idesc_f16(AQ, 16);            // P (TMEM) x ones (K-major, N = 16)
-        const uint64_t onesdesc = umma_smem_desc_sw128(smem_u32(smem_ones));
-#endif
+        // Everything that does not change is formed once: the descriptors of the Q tile, of the first K / V stage and of the
+        // ones tile, the S buffers' TMEM addresses; a stage's descriptor is then one add.  The round-2 wait-clock counters put
+        // this issue loop at ~1 000 clocks per key block (profiles/r2_attention.md); hoisting cut its instructions by a quarter and
+        // changed nothing measurable.  (The warp stays converged and elects the issuing lane per step: under a
+        // `lane == 0` branch ptxas wraps every uniform-datapath instruction in its own ELECT / BRA.U.ANY loop.)
+        {
+            constexpr uint32_t idesc_s = umma_idesc_f16(AQ, AK);            // Q (K-major) x K (K-major)
+            constexpr uint32_t idesc_o = umma_idesc_f16(AQ, AD, 1);         // P (TMEM) x V (MN-major)
+            constexpr uint32_t idesc_l = umma_idesc_f16(AQ, 16);            // P (TMEM) x ones (K-major, N = 16)
+            const uint64_t onesdesc = umma_smem_desc_sw128(smem_u32(smem_ones));
+            const uint64_t qdesc0 = umma_smem_desc_sw128(smem_u32(smem_q));
+            const uint64_t kdesc0 = umma_smem_desc_sw128(smem_u32(smem_k));
+            const uint64_t vdesc0 = umma_smem_desc_sw128_mn(smem_u32(smem_v));
+            const uint32_t tm_s = tmem_base + TM_S, tm_o = tmem_base + TM_O, tm_l = tmem_base + TM_L;
+            uint32_t g = 0, item_n = 0;                                     // g: running key-block counter
+            ItemWalk walk(p, blockIdx.x, gridDim.x, total_items);
+            while (walk.advance(p)) {
+                const Item it = walk.cur;
+                if (!it.valid()) continue;
+                const int nb = (it.len() + AK - 1) / AK;
+                const uint32_t qs = item_n % Q_STAGES;
+                const uint64_t qdesc = qdesc0 + (uint64_t) (qs * (kQBytes >> 4));
+                mbar_wait(&q_full[qs], (item_n / Q_STAGES) & 1);
+                for (int b = 0; b <= nb; ++b) {
+                    if (b < nb) {
+                        const uint32_t gb = g + b, st = gb % KV_STAGES;
+                        mbar_wait(&kv_full[st], (gb / KV_STAGES) & 1);
+                        tc_fence_after_sync();
+                        if (elect_one()) {
+                            const uint64_t kdesc = kdesc0 + (uint64_t) (st * (kKVBytes >> 4));
+                            const uint32_t d_tmem = tm_s + (gb & 1) * 64;
+#pragma unroll
+                            for (int k = 0; k < AD / 16; ++k) umma_f16_ss(d_tmem, qdesc + 2 * k, kdesc + 2 * k, idesc_s, k != 0);
+                            umma_commit(&s_full[gb & 1]);
+                            if (b == nb - 1) umma_commit(&q_empty[qs]);     // Q tile may be overwritten
+                        }
+                        __syncwarp();
+                    }
+                    if (b >= 1) {
+                        const uint32_t gp = g + b - 1, st = gp % KV_STAGES;
+                        mbar_wait(&p_ready[gp & 1], (gp >> 1) & 1);
+                        if (b == 1) mbar_wait(o_free, (item_n & 1) ^ 1);    // previous item's O has been read
+                        tc_fence_after_sync();
+                        if (elect_one()) {
+                            const uint64_t vdesc = vdesc0 + (uint64_t) (st * (kKVBytes >> 4));
+                            const uint32_t a_tmem = tm_s + (gp & 1) * 64;
+                            const uint32_t acc = b > 1 ? 1u : 0u;
+#pragma unroll
+                            for (int k = 0; k < AK / 16; ++k)                // 16 keys per step: 8 packed columns of P, 16 rows (2 KB) of V
+                                umma_f16_ts(tm_o, a_tmem + 8 * k, vdesc + (uint64_t) (128 * k), idesc_o, k > 0 ? 1u : acc);
+#pragma unroll
+                            for (int k = 0; k < AK / 16; ++k)                // row sums: P x ones
+                                umma_f16_ts(tm_l, a_tmem + 8 * k, onesdesc + 2 * k, idesc_l, k > 0 ? 1u : acc);
+                            umma_commit(&kv_empty[st]);
+                            umma_commit(&pv_done[gp & 1]);
+                        }
+                        __syncwarp();
+                    }
+                }
+                g += nb;
+                ++item_n;
+            }
+        }
         uint32_t g = 0, item_n = 0;                                     // g: running key-block counter
         ItemWalk walk(p, blockIdx.x, gridDim.x, total_items);
         while (walk.advance(p)) {
@@ -274,6 +331,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
             g += nb;
             ++item_n;
         }
+#endif
     } else {
         // ------------------------------------------------------------ softmax + output (4 warps)
         const int q = warp & 3;                               // TMEM lane quadrant of this warp

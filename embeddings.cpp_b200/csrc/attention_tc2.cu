@@ -201,6 +201,9 @@ attention_tc2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
         constexpr uint32_t idesc_l = umma_idesc_f16(AQ, 16);            // P (TMEM) x ones (K-major, N = 16)
         const uint64_t onesdesc = umma_smem_desc_sw128(smem_u32(smem_ones));
         const uint64_t qdesc = umma_smem_desc_sw128(smem_u32(smem_q));
+        // (a stage's descriptor is the first stage's plus a constant: formed once, as in attention_tc.cu)
+        const uint64_t kdesc0 = umma_smem_desc_sw128(smem_u32(smem_k));
+        const uint64_t vdesc0 = umma_smem_desc_sw128_mn(smem_u32(smem_v));
         uint32_t gv = 0, gkv = 0, item_n = 0;
         ItemWalk2 walk(p, blockIdx.x, gridDim.x, total_items);
         while (walk.advance(p)) {
@@ -217,7 +220,7 @@ attention_tc2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
                     if (hs == 0) mbar_wait(&kv_full[st], (kb / KV_STAGES) & 1);
                     tc_fence_after_sync();
                     if (elect_one()) {
-                        const uint64_t kdesc = umma_smem_desc_sw128(smem_u32(smem_k + st * kKVBytes));
+                        const uint64_t kdesc = kdesc0 + (uint64_t) (st * (kKVBytes >> 4));
                         const uint32_t d_tmem = tmem_base + TM_S + (g & 1) * 64;
 #pragma unroll
                         for (int k = 0; k < KS; ++k) {
@@ -237,7 +240,7 @@ attention_tc2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
                     tc_fence_after_sync();
                     if (elect_one()) {
                         // V tile [64 keys][64 columns] read MN-major; the second head of a pair starts 64 B into each row
-                        const uint64_t vdesc = umma_smem_desc_sw128_mn(smem_u32(smem_v + st * kKVBytes)) + (uint64_t) (hp * (D * 2 / 16));
+                        const uint64_t vdesc = vdesc0 + (uint64_t) (st * (kKVBytes >> 4) + hp * (D * 2 / 16));
                         const uint32_t a_tmem = tmem_base + TM_S + (g & 1) * 64;
                         const uint32_t o_tmem = tmem_base + TM_O + hp * D;
                         const uint32_t l_tmem = tmem_base + TM_L + hp * 16;
