@@ -128,6 +128,9 @@ __device__ __forceinline__ float2 ex2_poly2(float2 x) {
 #if BERT_ATTN_SPEC && !BERT_ATTN_MMASUM
 #error "BERT_ATTN_SPEC needs BERT_ATTN_MMASUM"
 #endif
+#if !BERT_ATTN_MMASUM
+#error "the MMA issuer always forms the row sums (P x ones): BERT_ATTN_MMASUM=0 is no longer built"
+#endif
 #ifndef BERT_ATTN_LDW
 #define BERT_ATTN_LDW 0
 #endif
@@ -277,61 +280,6 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                 ++item_n;
             }
         }
-        uint32_t g = 0, item_n = 0;                                     // g: running key-block counter
-        ItemWalk walk(p, blockIdx.x, gridDim.x, total_items);
-        while (walk.advance(p)) {
-            const Item it = walk.cur;
-            if (!it.valid()) continue;
-            const int len = it.len();
-            const int nb = (len + AK - 1) / AK;
-            const uint32_t qs = item_n % Q_STAGES;
-            mbar_wait(&q_full[qs], (item_n / Q_STAGES) & 1);
-            tc_fence_after_sync();
-            for (int b = 0; b <= nb; ++b) {
-                if (b < nb) {
-                    const uint32_t gb = g + b, st = gb % KV_STAGES;
-                    mbar_wait(&kv_full[st], (gb / KV_STAGES) & 1);
-                    tc_fence_after_sync();
-                    if (elect_one()) {
-                        const uint64_t adesc = umma_smem_desc_sw128(smem_u32(smem_q + qs * kQBytes));
-                        const uint64_t bdesc = umma_smem_desc_sw128(smem_u32(smem_k + st * kKVBytes));
-                        const uint32_t d_tmem = tmem_base + TM_S + (gb & 1) * 64;
-#pragma unroll
-                        for (int k = 0; k < AD / 16; ++k) umma_f16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc_s, k != 0);
-                        umma_commit(&s_full[gb & 1]);
-                        if (b == nb - 1) umma_commit(&q_empty[qs]);     // Q tile may be overwritten
-                    }
-                    __syncwarp();
-                }
-                if (b >= 1) {
-                    const uint32_t gp = g + b - 1, st = gp % KV_STAGES;
-                    mbar_wait(&p_ready[gp & 1], (gp >> 1) & 1);
-                    if (b == 1) mbar_wait(o_free, (item_n & 1) ^ 1);    // previous item's O has been read
-                    tc_fence_after_sync();
-                    if (elect_one()) {
-                        const uint64_t vdesc = umma_smem_desc_sw128_mn(smem_u32(smem_v + st * kKVBytes));
-                        const uint32_t a_tmem = tmem_base + TM_S + (gp & 1) * 64;
-#pragma unroll
-                        for (int k = 0; k < AK / 16; ++k) {
-                            // 16 keys per step: 8 packed columns of P, 16 rows (2 KB) of V
-                            umma_f16_ts(tmem_base + TM_O, a_tmem + 8 * k, vdesc + (uint64_t) (128 * k), idesc_o,
-                                        (b > 1 || k > 0) ? 1u : 0u);
-                        }
-#if BERT_ATTN_MMASUM
-#pragma unroll
-                        for (int k = 0; k < AK / 16; ++k)
-                            umma_f16_ts(tmem_base + TM_L, a_tmem + 8 * k, onesdesc + 2 * k, idesc_l, (b > 1 || k > 0) ? 1u : 0u);
-#endif
-                        umma_commit(&kv_empty[st]);
-                        umma_commit(&pv_done[gp & 1]);
-                    }
-                    __syncwarp();
-                }
-            }
-            g += nb;
-            ++item_n;
-        }
-#endif
     } else {
         // ------------------------------------------------------------ softmax + output (4 warps)
         const int q = warp & 3;                               // TMEM lane quadrant of this warp
