@@ -334,7 +334,7 @@ def main():
 
     cfg = base_config(args, shape, ftype, n_sent, n_tok, scaling, world)
     cfg.update({"tokens_per_step": T_all, "parallelism": f"dp{world} (sentence shards by shard_range, no collective)",
-                "l2": "inputs larger than L2: activations of one micro-batch are %.0f MB per buffer" % (min(T, 131072) * H * 2 / 1e6)})
+                "l2": "inputs larger than L2: activations of one micro-batch are %.0f MB per buffer" % (min(T, 262144) * H * 2 / 1e6)})
     if n_tok == 0:
         cfg["padded_vs_valid_tokens"] = round(padded_vs_valid(lens), 3)
         cfg["length_min_mean_max"] = [int(lens.min()), float(lens.mean()), int(lens.max())]

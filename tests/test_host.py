@@ -254,3 +254,20 @@ def test_quantizer_fails_loudly_without_a_gpu(pkg, tmp_path, capfd):
     assert "no CUDA device" in capfd.readouterr().err
     with pytest.raises(RuntimeError):
         pkg.quantize_file("/nonexistent", str(tmp_path / "o.bin"), 7)      # bad type is rejected first
+
+
+def test_text_pointer_table_round_trips(pkg):
+    """const char** built for bert_encode_batch: the numpy path (many short texts: one joined buffer + offsets) and the
+    item-by-item path (long or few texts) hand the same bytes to C."""
+    cases = [
+        [b"hello world", "café 一".encode(), b"", b"x" * 50] * 100,              # many short byte strings -> joined buffer
+        ["str one", b"bytes two", "你好"] * 120,                                  # str and bytes mixed
+        [b"y" * 1000] * 300,                                                              # long texts -> item by item
+        [b"few", b"texts"],                                                               # few texts -> item by item
+        [b"embedded\0nul", b"after"] * 200,                                               # C sees the text up to the first NUL
+    ]
+    for texts in cases:
+        p = pkg._text_ptrs(texts)
+        for i, t in enumerate(texts):
+            want = t if isinstance(t, bytes) else t.encode("utf-8")
+            assert p[i] == want.split(b"\0")[0]
