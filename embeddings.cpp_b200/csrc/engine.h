@@ -183,6 +183,7 @@ struct Engine {
     std::mutex q_mu;
     std::condition_variable q_cv;
     std::deque<MbTask> queue;
+    std::vector<int64_t> busy_tokens;          // per replica: tokens of the micro-batches it holds in flight (guarded by q_mu)
     bool stopping = false;
     HostPool pool;
 };

@@ -75,6 +75,27 @@ def test_tcgen05_gemm_with_fused_layernorm_epilogue(pkg, wt, M, N, K, epi):
     assert np.isfinite(err) and err <= tol, (err, ref)
 
 
+@pytest.mark.parametrize("wt,M,N,K", [(1, 600, 768, 768), (2, 515, 2304, 768), (3, 777, 512, 2048), (2, 1000, 384, 1536)])
+def test_tcgen05_gemm_against_numpy(pkg, wt, M, N, K):
+    """Per-kernel check against host arithmetic, not against another CUDA kernel: bertx_debug_gemm hands back the fp16 A
+    operand and the weights as decoded from the 4-bit planes (f32; the mainloop rounds d * q + m to fp16 once); numpy forms A W^T in f32 (what ggml's mul_mat computes for
+    these operands, ggml.c:11030-11258) and the tcgen05 kernel's fp16 output must match it to fp16 rounding."""
+    import ctypes
+    L = pkg.lib()
+    L.bertx_debug_gemm.restype = ctypes.c_int32
+    tc = np.zeros((1, M, N), dtype=np.float16)
+    ms = np.zeros(1, dtype=np.float32)
+    A = np.zeros((M, K), dtype=np.float16)
+    W = np.zeros((N, K), dtype=np.float32)
+    vp = lambda x: ctypes.c_void_p(x.ctypes.data)  # noqa: E731
+    rc = L.bertx_debug_gemm(M, N, K, wt, 0, 5, 1, None, vp(tc), vp(ms), None, None, vp(A), vp(W))
+    assert rc == 0
+    want = A.astype(np.float32) @ W.astype(np.float16).astype(np.float32).T     # the B operand is the fp16-rounded weight
+    got = tc[0].astype(np.float32)
+    assert np.isfinite(got).all() and np.abs(want).max() > 0.5
+    assert np.all(np.abs(got - want) <= 2e-3 * np.maximum(1.0, np.abs(want))), float(np.abs(got - want).max())
+
+
 ATTN_SHAPES = [(5, 64, 2, 64), (7, 200, 4, 64), (3, 512, 12, 64), (9, 130, 12, 32), (4, 512, 2, 32), (33, 17, 12, 64),
                (1, 1, 2, 32), (2, 2, 2, 64), (6, 97, 3, 64), (40, 384, 12, 64)]
 
