@@ -146,9 +146,9 @@ bool compare_h(const __half * da, const __half * db, size_t n, float * max_err, 
 struct TestWeight {
     DevBuf wbuf, nib, qd, qm;
     DevWeight w;
-    int build(int N, int K, int wtype, const float * d_bias, std::mt19937 & rng) {
+    int build(int N, int K, int wtype, const float * d_bias, std::mt19937 & rng, bool ln_target = false) {
         std::normal_distribution<float> nd(0.f, 1.f);
-        w.N = N; w.K = K; w.type = wtype; w.bias = d_bias; w.bn = gemm_pick_bn(N);
+        w.N = N; w.K = K; w.type = wtype; w.bias = d_bias; w.bn = ln_target ? gemm_pick_bn_ln(N) : gemm_pick_bn(N);
         const float wscale = 1.0f / sqrtf((float) K);
         if (wtype == W_F16) {
             std::vector<uint16_t> hw((size_t) N * K);
@@ -214,7 +214,7 @@ static int32_t gemm_test_impl(int32_t M, int32_t N, int32_t K, int32_t wtype, in
     cudaMemcpy(bias.p, hbias.data(), (size_t) N * 4, cudaMemcpyHostToDevice);
     cudaMemset(o1.p, 0xFF, (size_t) M * N * 2);
     TestWeight tw_;
-    { const int rc = tw_.build(N, K, wtype, bias.as<float>(), rng); if (rc) return rc; }
+    { const int rc = tw_.build(N, K, wtype, bias.as<float>(), rng, (epilogue & EPI_LN) != 0); if (rc) return rc; }
     DevWeight & w = tw_.w;
     CUtensorMap tma, tmo, tmr;
     if (!make_tmap_f16_2d(&tma, a.p, rows, K, 128)) return -4;
@@ -421,7 +421,7 @@ int32_t bertx_debug_gemm(int32_t M, int32_t N, int32_t K, int32_t wtype, int32_t
     for (auto & v : hbias) v = 0.5f * nd(rng);
     cudaMemcpy(bias.p, hbias.data(), (size_t) N * 4, cudaMemcpyHostToDevice);
     TestWeight tw;
-    { const int rc = tw.build(N, K, wtype, bias.as<float>(), rng); if (rc) return rc; }
+    { const int rc = tw.build(N, K, wtype, bias.as<float>(), rng, (epilogue & EPI_LN) != 0); if (rc) return rc; }
     CUtensorMap tma, tmo, tmr, tmo2;
     if (!make_tmap_f16_2d(&tma, a.p, rows, K, 128)) return -4;
     if (!make_tmap_f16_2d(&tmo, o1.p, M, N, 32)) return -4;

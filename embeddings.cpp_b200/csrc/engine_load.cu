@@ -68,8 +68,11 @@ const float * upload_vec(Replica & r, const TensorEntry & t) {
 }
 
 // Build one GEMM weight [sum(N_i)][K] from 1..3 file tensors stacked along N (Q|K|V share a GEMM).
+// ln_target: the GEMM is followed by residual + LayerNorm, which the epilogue can only absorb for 256- or 128-wide column blocks
+// held by one cluster (gemm_ln_fusable) -- so N = 384 (all-MiniLM, bge-small-en) takes three 128-wide blocks instead of two
+// 192-wide ones (unfused, the stand-alone LayerNorm kernel was 15 % of those models' step).
 bool build_weight(Replica & r, DevWeight & w, const TensorEntry * const * parts, const TensorEntry * const * biases,
-                  int n_parts, int K) {
+                  int n_parts, int K, bool ln_target = false) {
     int N = 0;
     for (int i = 0; i < n_parts; ++i) N += (int) parts[i]->ne[1];
     const int ft = parts[0]->ftype;
@@ -81,7 +84,7 @@ bool build_weight(Replica & r, DevWeight & w, const TensorEntry * const * parts,
     }
     w.N = N; w.K = K;
     w.type = ft <= 1 ? W_F16 : ft;
-    w.bn = gemm_pick_bn(N);
+    w.bn = ln_target ? gemm_pick_bn_ln(N) : gemm_pick_bn(N);
     if (w.bn == 0 || K % 64 != 0) {
         fprintf(stderr, "bert_load_from_file: unsupported GEMM shape N=%d K=%d (need N %% 64 == 0, K %% 64 == 0)\n", N, K);
         return false;
@@ -320,9 +323,9 @@ bool Engine::upload(Replica & r, const ModelFile & mf) {
         const TensorEntry * qkv_w[3] = {qw, kw, vw};
         const TensorEntry * qkv_b[3] = {qb, kb, vb};
         if (!build_weight(r, L.qkv, qkv_w, qkv_b, 3, H)) return false;
-        if (!build_weight(r, L.o, &ow, &ob, 1, H)) return false;
+        if (!build_weight(r, L.o, &ow, &ob, 1, H, true)) return false;
         if (!build_weight(r, L.ffi, &iw, &ib, 1, H)) return false;
-        if (!build_weight(r, L.ffo, &fw, &fb, 1, I)) return false;
+        if (!build_weight(r, L.ffo, &fw, &fb, 1, I, true)) return false;
         L.ln_att_g = upload_vec(r, *ag); L.ln_att_b = upload_vec(r, *ab);
         L.ln_out_g = upload_vec(r, *og); L.ln_out_b = upload_vec(r, *obb);
         if (!L.ln_att_g || !L.ln_att_b || !L.ln_out_g || !L.ln_out_b) return false;

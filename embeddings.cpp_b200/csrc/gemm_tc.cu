@@ -881,6 +881,16 @@ int gemm_pick_bn(int N) {
     return 0;
 }
 
+// Column-block width for a weight whose GEMM is followed by residual + LayerNorm: the fused epilogue exists for 256- and
+// 128-wide blocks held by one cluster of at most 4 CTA pairs, so N = 384 (all-MiniLM, bge-small-en) takes three 128-wide
+// blocks rather than gemm_pick_bn's two 192-wide ones.
+int gemm_pick_bn_ln(int N) {
+    static const bool on = [] { const char * e = getenv("BERT_LN_BN128"); return !e || atoi(e) != 0; }();   // 0: A/B against the unfused form
+    const int bn = gemm_pick_bn(N);
+    if (on && bn != 256 && bn != 128 && N % 128 == 0 && N / 128 <= 4) return 128;
+    return bn;
+}
+
 bool gemm_ln_fusable(const DevWeight & w) {
     // the cluster must hold every column block of a row stripe: N / BN pairs, at most 4 (8 CTAs)
     return (w.bn == 256 || w.bn == 128) && w.N / w.bn <= 4 && w.bias != nullptr;

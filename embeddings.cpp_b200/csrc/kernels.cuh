@@ -59,7 +59,8 @@ struct GemmArgs {
     int bn_override = 0;
 };
 
-int gemm_pick_bn(int N);              // N-tile (256/192/128/64) used for a weight with N rows
+int gemm_pick_bn(int N);                 // N-tile (256/192/128/64) used for a weight with N rows
+int gemm_pick_bn_ln(int N);              // the same for a GEMM followed by residual + LayerNorm (prefers the fusable widths 256 / 128)
 cudaError_t launch_gemm_tc(const GemmArgs & g, int num_sms, cudaStream_t st);
 bool gemm_ln_fusable(const DevWeight & w);   // can the LayerNorm after this GEMM run in its epilogue?
 cudaError_t launch_gemm_simt(const GemmArgs & g, cudaStream_t st);      // validation kernel

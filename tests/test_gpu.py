@@ -67,6 +67,7 @@ def test_tcgen05_gemm_with_q8_fakequant_epilogue(pkg, wt, M, N, K, epi):
 @pytest.mark.parametrize("wt,M,N,K,epi", [
     (1, 600, 768, 768, 21), (2, 1000, 768, 768, 29), (3, 777, 768, 3072, 29), (2, 515, 512, 1536, 29),
     (2, 300, 256, 256, 21), (1, 131, 128, 512, 29), (2, 70000, 768, 768, 29), (2, 600, 1024, 1024, 29), (1, 300, 1024, 512, 21),
+    (2, 900, 384, 384, 29), (2, 1300, 384, 1536, 29), (1, 700, 384, 384, 21), (1, 515, 384, 1536, 29), (3, 40000, 384, 1536, 29),   # three 128-wide blocks
 ])
 def test_tcgen05_gemm_with_fused_layernorm_epilogue(pkg, wt, M, N, K, epi):
     rc, err, ref = pkg.selftest_gemm(M, N, K, wt, epi, seed=5)
