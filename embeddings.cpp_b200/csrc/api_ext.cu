@@ -28,9 +28,12 @@ int32_t bertx_stage(struct bert_ctx * ctx, int32_t dev, int32_t n_sent, const be
     std::vector<int32_t> ids(src_off[n_sent]);
     std::vector<int32_t> cu;
     r.job_cu_off.clear();
+    r.job_nspans.clear();
+    std::vector<int32_t> spans;
     size_t t = 0;
     for (const MicroBatch & mb : r.job_mbs) {
         r.job_cu_off.push_back(cu.size());
+        const size_t k0 = cu.size();
         int local = 0;
         for (int i = 0; i < mb.count; ++i) {
             const int idx = r.job_order[mb.first + i];
@@ -39,6 +42,11 @@ int32_t bertx_stage(struct bert_ctx * ctx, int32_t dev, int32_t n_sent, const be
             t += n_tokens[idx]; local += n_tokens[idx];
         }
         cu.push_back(local);
+        // the micro-batch's span boundaries follow its cu_seqlens, as in the staging slots of the encode path
+        spans.assign((size_t) mb.count + 1, 0);
+        const int ns = pack_spans(cu.data() + k0, mb.count, spans.data());
+        cu.insert(cu.end(), spans.begin(), spans.begin() + ns + 1);
+        r.job_nspans.push_back(ns);
     }
     if (!cuda_ok(cudaMalloc((void **) &r.job_ids, ids.size() * 4 + 256), "cudaMalloc job ids")) return -4;
     if (!cuda_ok(cudaMalloc((void **) &r.job_cu, cu.size() * 4 + 256), "cudaMalloc job cu")) return -4;
@@ -53,7 +61,7 @@ static bool run_job_once(Engine & e, Replica & r) {
     for (size_t k = 0; k < r.job_mbs.size(); ++k) {
         const MicroBatch & mb = r.job_mbs[k];
         if (!e.forward(r, r.job_ids + mb.tok_offset, r.job_cu + r.job_cu_off[k], mb.count, mb.tokens, mb.max_len,
-                       r.job_out + (size_t) mb.first * e.hp.n_embd)) return false;
+                       r.job_out + (size_t) mb.first * e.hp.n_embd, r.job_nspans[k])) return false;
     }
     return true;
 }
@@ -317,7 +325,7 @@ int32_t bertx_selftest_attention(int32_t n_sent, int32_t max_len, int32_t n_head
             }
         }
     }
-    DevBuf qkv, dcu, o1, o2;
+    DevBuf qkv, dcu, o1, o2, dspan, dtb;
     if (!qkv.alloc(hq.size() * 2) || !dcu.alloc(cu.size() * 4) || !o1.alloc(T * H * 2) || !o2.alloc(T * H * 2)) return -3;
     cudaMemcpy(qkv.p, hq.data(), hq.size() * 2, cudaMemcpyHostToDevice);
     cudaMemcpy(dcu.p, cu.data(), cu.size() * 4, cudaMemcpyHostToDevice);
@@ -331,6 +339,17 @@ int32_t bertx_selftest_attention(int32_t n_sent, int32_t max_len, int32_t n_head
         const int impl = d_head != 64 ? 1 : (seed & 2048) ? 0 : (seed & 4096) ? 1 : (seed & 8192) ? 3 : attn_impl_for(d_head);
         cudaError_t ae;
         if (impl == 3) ae = launch_attention_tc3(&tq, &tkv, dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0);
+        else if (impl == 1 && !(seed & 16384)) {
+            // as the engine runs it: short sentences packed into spans (bit 14 of the seed: one work item per sentence)
+            std::vector<int32_t> span(n_sent + 1);
+            const int ns = pack_spans(cu.data(), n_sent, span.data());
+            std::vector<int2> tb(T);
+            for (int i = 0; i < n_sent; ++i) for (int t = cu[i]; t < cu[i + 1]; ++t) tb[t] = make_int2(cu[i], cu[i + 1]);
+            if (!dspan.alloc(span.size() * 4) || !dtb.alloc(tb.size() * 8)) return -3;
+            cudaMemcpy(dspan.p, span.data(), (size_t) (ns + 1) * 4, cudaMemcpyHostToDevice);
+            cudaMemcpy(dtb.p, tb.data(), tb.size() * 8, cudaMemcpyHostToDevice);
+            ae = launch_attention_tc2(&tq, &tkv, dspan.as<int32_t>(), ns, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0, dtb.as<int2>());
+        }
         else if (impl == 1) ae = launch_attention_tc2(&tq, &tkv, dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0);
         else ae = launch_attention_tc(&tq, &tkv, dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0);
         if (!cuda_ok(ae, "selftest attention launch")) return -6;
@@ -366,7 +385,19 @@ int32_t bertx_bench_attention(int32_t n_sent, int32_t len, int32_t n_head, int32
     CUtensorMap tq, tkv;
     if (!make_attention_tmaps(&tq, &tkv, qkv.as<__half>(), T, H)) return -4;
     const int impl = attn_impl_for(d_head);
+    DevBuf dspan, dtb;
+    int ns = 0;
+    if (impl == 1 && !getenv("BERT_ATTN_NOPACK")) {               // as the engine runs it: short sentences packed into spans
+        std::vector<int32_t> span(n_sent + 1);
+        ns = pack_spans(cu.data(), n_sent, span.data());
+        std::vector<int2> tb(T);
+        for (int i = 0; i < n_sent; ++i) for (int t = cu[i]; t < cu[i + 1]; ++t) tb[t] = make_int2(cu[i], cu[i + 1]);
+        if (!dspan.alloc(span.size() * 4) || !dtb.alloc(tb.size() * 8)) return -3;
+        cudaMemcpy(dspan.p, span.data(), (size_t) (ns + 1) * 4, cudaMemcpyHostToDevice);
+        cudaMemcpy(dtb.p, tb.data(), tb.size() * 8, cudaMemcpyHostToDevice);
+    }
     auto launch = [&]() {
+        if (impl == 1 && ns > 0) return launch_attention_tc2(&tq, &tkv, dspan.as<int32_t>(), ns, len, n_head, d_head, o1.as<__half>(), W_Q4_0, prop.multiProcessorCount, 0, dtb.as<int2>());
         if (impl == 3) return launch_attention_tc3(&tq, &tkv, dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, prop.multiProcessorCount, 0);
         if (impl == 1) return launch_attention_tc2(&tq, &tkv, dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, prop.multiProcessorCount, 0);
         return launch_attention_tc(&tq, &tkv, dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, prop.multiProcessorCount, 0);

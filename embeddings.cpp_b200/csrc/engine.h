@@ -95,7 +95,8 @@ struct Replica {
     CUtensorMap tr_x, tr_x1;                         // residual maps (box 64 x 32, epilogue TMA loads)
     static const int kSlots = 3;
     int32_t * d_ids[kSlots] = {};                    // [t_cap]
-    int32_t * d_cu[kSlots] = {};                     // [b_cap+1]
+    int32_t * d_cu[kSlots] = {};                     // [2 (b_cap+1)]: cu_seqlens [n+1], then the span boundaries of pack_spans [n_spans+1]
+    int2 * tok_bounds = nullptr;                     // [t_cap] per token: [first, end) token of its sentence (written by embed_ln)
     float * d_out[kSlots] = {};                      // [b_cap][H] f32
     int32_t * h_ids[kSlots] = {};                    // pinned mirrors
     int32_t * h_cu[kSlots] = {};
@@ -108,7 +109,8 @@ struct Replica {
     std::vector<MicroBatch> job_mbs;
     std::vector<int> job_order;               // job position -> caller's sentence index
     int32_t * job_ids = nullptr;
-    int32_t * job_cu = nullptr;               // concatenated per-micro-batch cu arrays
+    int32_t * job_cu = nullptr;               // concatenated per-micro-batch cu arrays (each followed by its span boundaries)
+    std::vector<int> job_nspans;              // spans per micro-batch
     float * job_out = nullptr;                // [n_sent][H]
     int job_sent = 0;
     std::vector<size_t> job_cu_off;
@@ -126,7 +128,7 @@ struct Engine {
     std::mutex mu;                             // a context is not re-entrant (bert.h note)
     std::atomic<int64_t> launches{0};
     int fq_type = -1;                          // W_Q4_0 / W_Q4_1 when activation fake-quant is on
-    bool gemm_simt = false, attn_ref = false, attn_v2 = false, attn_v3 = false;
+    bool gemm_simt = false, attn_ref = false, attn_v2 = false, attn_v3 = false, attn_pack = true;
     bool fuse_ln_att = true;                   // also fuse the LayerNorm after the attention-output GEMM (BERT_FUSE_LN=1: ffn-out only)
     bool fuse_ln = true;                       // LayerNorm in the epilogue of the o / ffn-out GEMMs (BERT_FUSE_LN=0 disables)  // validation kernels forced by env (debug only)
     int t_cap = 0, b_cap = 0;
@@ -142,8 +144,9 @@ struct Engine {
     void free_job(Replica & r);
 
     // enqueue the forward of one micro-batch whose ids / cu are already on the device
+    // n_spans > 0: d_cu[n_sent + 1 ..] holds the boundaries of n_spans packed spans (pack_spans)
     bool forward(Replica & r, const int32_t * d_ids, const int32_t * d_cu, int n_sent, int T, int max_len,
-                 float * d_out);
+                 float * d_out, int n_spans = 0);
 
     // order sentences by length (descending) and cut into micro-batches
     void plan(const int32_t * n_tokens, int n, std::vector<int> & order, std::vector<MicroBatch> & mbs) const;

@@ -201,6 +201,7 @@ bool Engine::init_devices(const ModelFile & mf) {
     if (devs.empty()) for (int i = 0; i < n_dev; ++i) devs.push_back(i);
 
     if (const char * e = getenv("BERT_GEMM_IMPL")) gemm_simt = strcmp(e, "simt") == 0;
+    if (const char * e = getenv("BERT_ATTN_PACK")) attn_pack = atoi(e) != 0;
     if (const char * e = getenv("BERT_FUSE_LN")) { fuse_ln = atoi(e) != 0; fuse_ln_att = atoi(e) >= 2; }
     if (const char * e = getenv("BERT_ATTN_IMPL")) { attn_ref = strcmp(e, "ref") == 0; attn_v2 = strcmp(e, "tc2") == 0; attn_v3 = strcmp(e, "tc3") == 0; }
     fq_type = (hp.ftype == W_Q4_0 || hp.ftype == W_Q4_1) ? hp.ftype : -1;
@@ -365,12 +366,14 @@ bool Engine::alloc_workspace(Replica & r) {
         fprintf(stderr, "bert_load_from_file: cuTensorMapEncodeTiled failed for an activation map\n");
         return false;
     }
+    r.tok_bounds = dev_alloc<int2>(r, t_cap);
+    if (!r.tok_bounds) return false;
     for (int s = 0; s < Replica::kSlots; ++s) {
         r.d_ids[s] = dev_alloc<int32_t>(r, t_cap);
-        r.d_cu[s] = dev_alloc<int32_t>(r, b_cap + 1);
+        r.d_cu[s] = dev_alloc<int32_t>(r, 2 * (b_cap + 1));
         r.d_out[s] = dev_alloc<float>(r, (size_t) b_cap * H);
         r.h_ids[s] = pinned_alloc<int32_t>(r, t_cap);
-        r.h_cu[s] = pinned_alloc<int32_t>(r, b_cap + 1);
+        r.h_cu[s] = pinned_alloc<int32_t>(r, 2 * (b_cap + 1));
         r.h_out[s] = pinned_alloc<float>(r, (size_t) b_cap * H);
         if (!r.d_ids[s] || !r.d_cu[s] || !r.d_out[s] || !r.h_ids[s] || !r.h_cu[s] || !r.h_out[s]) return false;
         if (!cuda_ok(cudaEventCreateWithFlags(&r.slot_done[s], cudaEventDisableTiming | cudaEventBlockingSync), "cudaEventCreate")) return false;

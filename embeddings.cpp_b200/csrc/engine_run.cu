@@ -28,7 +28,7 @@ struct Launcher {
 //   residual [1040-1045]  ->  LN [1047-1056]  ->  GEMM ffn-in + bias + GELU [1059-1063]  ->
 //   GEMM ffn-out + bias + residual [1066-1071]  ->  LN [1073-1082]
 bool Engine::forward(Replica & r, const int32_t * d_ids, const int32_t * d_cu, int n_sent, int T, int max_len,
-                     float * d_out) {
+                     float * d_out, int n_spans) {
     const int H = hp.n_embd;
     const bool fq = fq_type >= 0;
     cudaStream_t st = r.stream;
@@ -67,8 +67,12 @@ bool Engine::forward(Replica & r, const int32_t * d_ids, const int32_t * d_cu, i
         end();
     };
     begin(KK_EMBED);
+    // packed spans (head size 32 kernel): several short sentences share one attention work item; the embedding kernel
+    // leaves every token's sentence bounds behind for the masks.  BERT_ATTN_PACK=0 turns it off (A/B).
+    const int dh_ = H / hp.n_head;
+    const bool packed = n_spans > 0 && n_spans < n_sent && attn_pack && !attn_ref && !(dh_ == 64 && !attn_v2);
     L(KK_EMBED, launch_embed_ln(r.word, r.postype, r.ln_e_g, r.ln_e_b, d_ids, d_cu, n_sent, T, H,
-                                r.x, fq ? r.xq : nullptr, fq_type, st), "embed_ln");
+                                r.x, fq ? r.xq : nullptr, fq_type, packed ? r.tok_bounds : nullptr, st), "embed_ln");
     end();
     for (int il = 0; il < hp.n_layer && L.ok; ++il) {
         const LayerDev & ly = r.layers[il];
@@ -82,7 +86,10 @@ bool Engine::forward(Replica & r, const int32_t * d_ids, const int32_t * d_cu, i
             // profiles/r2_attention.md) | ref (SIMT validation kernel)
             if (attn_ref) ae = launch_attention_ref(r.qkv, d_cu, n_sent, max_len, hp.n_head, dh, r.ctx, fq_type, st);
             else if (dh == 64 && attn_v3) ae = launch_attention_tc3(&r.ta_q, &r.ta_kv, d_cu, n_sent, max_len, hp.n_head, dh, r.ctx, fq_type, r.num_sms, st);
-            else if (dh == 32 || attn_v2) ae = launch_attention_tc2(&r.ta_q, &r.ta_kv, d_cu, n_sent, max_len, hp.n_head, dh, r.ctx, fq_type, r.num_sms, st);
+            else if (dh == 32 || attn_v2) {
+                if (packed) ae = launch_attention_tc2(&r.ta_q, &r.ta_kv, d_cu + n_sent + 1, n_spans, max_len, hp.n_head, dh, r.ctx, fq_type, r.num_sms, st, r.tok_bounds);
+                else ae = launch_attention_tc2(&r.ta_q, &r.ta_kv, d_cu, n_sent, max_len, hp.n_head, dh, r.ctx, fq_type, r.num_sms, st);
+            }
             else ae = launch_attention_tc(&r.ta_q, &r.ta_kv, d_cu, n_sent, max_len, hp.n_head, dh, r.ctx, fq_type, r.num_sms, st);
             L(KK_ATTN, ae, "attention");
         }

@@ -78,7 +78,7 @@ struct DevTable {
 cudaError_t launch_embed_ln(const DevTable & word, const float * postype /*[n_max][H] f32*/,
                             const float * gamma, const float * beta,
                             const int32_t * ids, const int32_t * cu_seqlens, int n_sent, int T, int H,
-                            __half * out, __half * out_fq, int fq_type, cudaStream_t st);
+                            __half * out, __half * out_fq, int fq_type, int2 * tok_bounds, cudaStream_t st);
 
 // K3: y = LN(x) * g + b, x already holds GEMM + bias + residual (fp16)
 cudaError_t launch_ln(const __half * x, const float * gamma, const float * beta, int T, int H,
@@ -93,15 +93,21 @@ bool make_attention_tmaps(CUtensorMap * tm_q, CUtensorMap * tm_kv, const __half 
 cudaError_t launch_attention_tc(const CUtensorMap * tm_q, const CUtensorMap * tm_kv, const int32_t * cu_seqlens,
                                 int n_sent, int max_len, int n_head, int d_head, __half * out, int fq_type,
                                 int num_sms, cudaStream_t st);
-// round-2 kernel (attention_tc2.cu): head sizes 64 and 32 (two heads per work item), eight softmax warps per CTA; same maps
+// round-2 kernel (attention_tc2.cu): head sizes 64 and 32 (two heads per work item), eight softmax warps per CTA; same maps.
+// With tok_bounds (per token: [first, end) token of its sentence, written by launch_embed_ln) `cu_seqlens` may hold SPANS of
+// several whole sentences of at most 128 tokens in total (pack_spans): one work item then serves all of them, every query row
+// masked to the keys of its own sentence.
 cudaError_t launch_attention_tc2(const CUtensorMap * tm_q, const CUtensorMap * tm_kv, const int32_t * cu_seqlens,
                                  int n_sent, int max_len, int n_head, int d_head, __half * out, int fq_type,
-                                 int num_sms, cudaStream_t st);
+                                 int num_sms, cudaStream_t st, const int2 * tok_bounds = nullptr);
 // round-2 kernel for head size 64 (attention_tc3.cu): three S buffers in TMEM, separate K / V rings, software-pipelined softmax
 cudaError_t launch_attention_tc3(const CUtensorMap * tm_q, const CUtensorMap * tm_kv, const int32_t * cu_seqlens,
                                  int n_sent, int max_len, int n_head, int d_head, __half * out, int fq_type,
                                  int num_sms, cudaStream_t st);
 void attn3_prof_fetch(unsigned long long * out);      // diagnostic counters of a -DBERT_ATTN3_PROF=1 build
+// Greedy packing of consecutive sentences into spans of at most 128 tokens (a longer sentence is a span of its own):
+// span_cu[0 .. n_spans] = token offsets of the span boundaries; returns n_spans.  Host code.
+int pack_spans(const int32_t * cu_seqlens, int n_sent, int32_t * span_cu);
 cudaError_t launch_attention_ref(const __half * qkv, const int32_t * cu_seqlens, int n_sent, int max_len,
                                  int n_head, int d_head, __half * out, int fq_type, cudaStream_t st);
 

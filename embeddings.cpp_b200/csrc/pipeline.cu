@@ -141,12 +141,13 @@ bool Engine::slot_submit(Replica & r, int s, MbTask & t, bool notify) {
         off += t.len[i];
     }
     cu[n] = off;
+    const int n_spans = pack_spans(cu, n, cu + n + 1);       // short sentences share attention work items (kernels.cuh)
     const int H = hp.n_embd;
     bool ok = cuda_ok(cudaMemcpyAsync(r.d_ids[s], ids, (size_t) off * 4, cudaMemcpyHostToDevice, r.copy_in), "H2D ids");
-    ok = ok && cuda_ok(cudaMemcpyAsync(r.d_cu[s], cu, (size_t) (n + 1) * 4, cudaMemcpyHostToDevice, r.copy_in), "H2D cu");
+    ok = ok && cuda_ok(cudaMemcpyAsync(r.d_cu[s], cu, (size_t) (n + 1 + n_spans + 1) * 4, cudaMemcpyHostToDevice, r.copy_in), "H2D cu");
     ok = ok && cuda_ok(cudaEventRecord(r.h2d_done[s], r.copy_in), "event record");
     ok = ok && cuda_ok(cudaStreamWaitEvent(r.stream, r.h2d_done[s], 0), "stream wait");
-    ok = ok && forward(r, r.d_ids[s], r.d_cu[s], n, off, t.max_len, r.d_out[s]);
+    ok = ok && forward(r, r.d_ids[s], r.d_cu[s], n, off, t.max_len, r.d_out[s], n_spans);
     ok = ok && cuda_ok(cudaEventRecord(r.fwd_done[s], r.stream), "event record");
     ok = ok && cuda_ok(cudaStreamWaitEvent(r.copy_out, r.fwd_done[s], 0), "stream wait");
     ok = ok && cuda_ok(cudaMemcpyAsync(r.h_out[s], r.d_out[s], (size_t) n * H * 4, cudaMemcpyDeviceToHost, r.copy_out), "D2H out");
@@ -203,10 +204,11 @@ bool Engine::run_inline(Replica & r, MbTask & t) {
         off += t.len[i];
     }
     cu[n] = off;
+    const int n_spans = pack_spans(cu, n, cu + n + 1);
     const size_t H = (size_t) hp.n_embd;
     bool ok = cuda_ok(cudaMemcpyAsync(r.d_ids[0], ids, (size_t) off * 4, cudaMemcpyHostToDevice, r.stream), "H2D ids");
-    ok = ok && cuda_ok(cudaMemcpyAsync(r.d_cu[0], cu, (size_t) (n + 1) * 4, cudaMemcpyHostToDevice, r.stream), "H2D cu");
-    ok = ok && forward(r, r.d_ids[0], r.d_cu[0], n, off, t.max_len, r.d_out[0]);
+    ok = ok && cuda_ok(cudaMemcpyAsync(r.d_cu[0], cu, (size_t) (n + 1 + n_spans + 1) * 4, cudaMemcpyHostToDevice, r.stream), "H2D cu");
+    ok = ok && forward(r, r.d_ids[0], r.d_cu[0], n, off, t.max_len, r.d_out[0], n_spans);
     ok = ok && cuda_ok(cudaMemcpyAsync(r.h_out[0], r.d_out[0], (size_t) n * H * 4, cudaMemcpyDeviceToHost, r.stream), "D2H out");
     ok = cuda_ok(cudaStreamSynchronize(r.stream), "stream sync") && ok;
     if (!ok) { cudaGetLastError(); return false; }

@@ -126,7 +126,7 @@ __global__ void __launch_bounds__(ROWS_PER_CTA * 32)
 embed_ln_kernel(const DevTable word, const float * __restrict__ postype,
                 const float * __restrict__ gamma, const float * __restrict__ beta,
                 const int32_t * __restrict__ ids, const int32_t * __restrict__ cu, int n_sent, int T, int H,
-                __half * __restrict__ out, __half * __restrict__ out_fq, int fq_type) {
+                __half * __restrict__ out, __half * __restrict__ out_fq, int fq_type, int2 * __restrict__ tok_bounds) {
     pdl_launch_dependents();
     pdl_wait();
     const int row = blockIdx.x * ROWS_PER_CTA + (threadIdx.x >> 5);
@@ -178,7 +178,11 @@ embed_ln_kernel(const DevTable word, const float * __restrict__ postype,
         lo += kk * step;
         hi = min(hi, lo + step);
     }
-    const int pos = row - __ldg(cu + lo);
+    const int sent_t0 = __ldg(cu + lo);
+    const int pos = row - sent_t0;
+    // by-product for the attention kernel that packs several short sentences into one work item: [first, end) token of this
+    // token's sentence
+    if (tok_bounds != nullptr && lane == 0) tok_bounds[row] = make_int2(sent_t0, __ldg(cu + lo + 1));
     float s = 0.f;
 #pragma unroll
     for (int i = 0; i < NCH; ++i) {
@@ -254,12 +258,12 @@ pool_norm_kernel(const __half * __restrict__ x, const int32_t * __restrict__ cu,
 
 cudaError_t launch_embed_ln(const DevTable & word, const float * postype, const float * gamma, const float * beta,
                             const int32_t * ids, const int32_t * cu_seqlens, int n_sent, int T, int H,
-                            __half * out, __half * out_fq, int fq_type, cudaStream_t st) {
+                            __half * out, __half * out_fq, int fq_type, int2 * tok_bounds, cudaStream_t st) {
     if (T <= 0) return cudaSuccess;
     const int grid = (T + ROWS_PER_CTA - 1) / ROWS_PER_CTA;
     const int nch = (H / 8 + 31) / 32;
 #define EMBED_LAUNCH(NCH_) launch_pdl(embed_ln_kernel<NCH_>, dim3(grid), dim3(ROWS_PER_CTA * 32), 0, st, \
-        word, postype, gamma, beta, ids, cu_seqlens, n_sent, T, H, out, out_fq, fq_type)
+        word, postype, gamma, beta, ids, cu_seqlens, n_sent, T, H, out, out_fq, fq_type, tok_bounds)
     if (nch <= 1) return EMBED_LAUNCH(1);
     if (nch == 2) return EMBED_LAUNCH(2);
     if (nch == 3) return EMBED_LAUNCH(3);

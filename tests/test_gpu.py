@@ -98,16 +98,18 @@ def test_tcgen05_gemm_against_numpy(pkg, wt, M, N, K):
 
 
 ATTN_SHAPES = [(5, 64, 2, 64), (7, 200, 4, 64), (3, 512, 12, 64), (9, 130, 12, 32), (4, 512, 2, 32), (33, 17, 12, 64),
-               (1, 1, 2, 32), (2, 2, 2, 64), (6, 97, 3, 64), (40, 384, 12, 64)]
+               (1, 1, 2, 32), (2, 2, 2, 64), (6, 97, 3, 64), (40, 384, 12, 64),
+               (200, 30, 12, 32), (64, 70, 12, 32), (300, 9, 6, 32), (150, 128, 4, 32)]     # many short sentences: packed spans
 
 
 @pytest.mark.parametrize("n_sent,L,nh,d", ATTN_SHAPES)
-@pytest.mark.parametrize("flags", [0, 1024, 2048, 2048 + 1024, 4096, 4096 + 1024, 8192, 8192 + 1024],
-                         ids=["default", "default-ramp", "tc1", "tc1-ramp", "8warp", "8warp-ramp", "3buf", "3buf-ramp"])
+@pytest.mark.parametrize("flags", [0, 1024, 2048, 2048 + 1024, 4096, 4096 + 1024, 8192, 8192 + 1024, 4096 + 16384],
+                         ids=["default", "default-ramp", "tc1", "tc1-ramp", "8warp", "8warp-ramp", "3buf", "3buf-ramp", "8warp-unpacked"])
 def test_fused_attention_matches_reference_kernel(pkg, n_sent, L, nh, d, flags):
     """Seed bit 10: key rows grow along the sentence, so the running max keeps leaving the 2^8 window (the rescale / redo path);
     bit 11: attention_tc.cu (head size 64; head size 32 always runs attention_tc2.cu); bit 12: attention_tc2.cu; bit 13: attention_tc3.cu; none: the
-    engine's dispatch."""
+    engine's dispatch.  attention_tc2.cu packs short sentences into spans of <= 128 tokens as the engine does (bit 14: one work
+    item per sentence)."""
     rc, err, ref = pkg.selftest_attention(n_sent, L, nh, d, seed=(L % 1024) | flags)
     assert rc == 0
     assert np.isfinite(err) and err <= 6e-3 * max(ref, 1.0), (err, ref)
@@ -126,9 +128,11 @@ def test_encode_matches_reference_golden_embeddings(models, path):
     got2 = m.forward_tokens(toks)
     cos, err = cos_and_maxabs(got2, g["emb_forward"])
     assert cos >= COS_MIN and err <= MAX_ABS[ft], (ft, cos, err)
-    # batch-composition invariance: packing replaces padding, so only rounding may differ
+    # batch-composition invariance: packing replaces padding, so only rounding may differ.  (Head size 32: short sentences
+    # share attention work items, so where a sentence's keys fall in the 64-key blocks -- and with it the reference max its
+    # fp16 P values are rounded against -- depends on its neighbours: differences at the level of that rounding, 1e-4.)
     got3 = np.concatenate([m.forward_tokens([t]) for t in toks[:6]])
-    assert np.abs(got3 - got2[:6]).max() <= (1e-5 if ft in ("f32", "f16") else 4e-3)
+    assert np.abs(got3 - got2[:6]).max() <= (3e-4 if ft in ("f32", "f16") else 4e-3)
     assert np.array_equal(m.forward_tokens(toks[:5], fake_batch=True), m.forward_tokens(toks[:5]))
 
 
@@ -212,10 +216,24 @@ def test_staged_job_equals_encode_and_multi_microbatch(pkg):
         m.stage(ids, lens)
         ms, staged = m.run_staged(reps=2, fetch=True)
         enc = m.encode(texts)
-        assert ms > 0 and np.array_equal(staged, enc)
+        # the two paths cut the job into different micro-batches; with short sentences packed into shared attention work
+        # items (head size 32) a sentence's neighbours decide where its keys fall in the 64-key blocks, so the results agree
+        # to the rounding of the fp16 P values / one q8 step, not bit for bit ...
+        assert ms > 0 and np.abs(staged - enc).max() <= 4e-3
+        assert np.array_equal(m.encode(texts), enc)                  # ... while the same call is bit-identical from run to run
         prof = m.profile_staged()
         assert prof["gemm"][1] > 0 and prof["attention"][1] > 0 and m.kernel_launches() > 0
         m.close()
+        # ... and without the packing every sentence is computed on its own: any cut gives the same bits
+        os.environ["BERT_ATTN_PACK"] = "0"
+        try:
+            m = pkg.BertModel(model)
+            m.stage(ids, lens)
+            _, staged = m.run_staged(reps=1, fetch=True)
+            assert np.array_equal(staged, m.encode(texts))
+            m.close()
+        finally:
+            del os.environ["BERT_ATTN_PACK"]
     finally:
         del os.environ["BERT_MICROBATCH_TOKENS"]
     m2 = pkg.BertModel(model)
