@@ -339,7 +339,7 @@ int32_t bertx_selftest_attention(int32_t n_sent, int32_t max_len, int32_t n_head
         const int impl = d_head != 64 ? 1 : (seed & 2048) ? 0 : (seed & 4096) ? 1 : (seed & 8192) ? 3 : attn_impl_for(d_head);
         cudaError_t ae;
         if (impl == 3) ae = launch_attention_tc3(&tq, &tkv, dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0);
-        else if (impl == 1 && !(seed & 16384)) {
+        else if (!(seed & 16384)) {
             // as the engine runs it: short sentences packed into spans (bit 14 of the seed: one work item per sentence)
             std::vector<int32_t> span(n_sent + 1);
             const int ns = pack_spans(cu.data(), n_sent, span.data());
@@ -348,7 +348,8 @@ int32_t bertx_selftest_attention(int32_t n_sent, int32_t max_len, int32_t n_head
             if (!dspan.alloc(span.size() * 4) || !dtb.alloc(tb.size() * 8)) return -3;
             cudaMemcpy(dspan.p, span.data(), (size_t) (ns + 1) * 4, cudaMemcpyHostToDevice);
             cudaMemcpy(dtb.p, tb.data(), tb.size() * 8, cudaMemcpyHostToDevice);
-            ae = launch_attention_tc2(&tq, &tkv, dspan.as<int32_t>(), ns, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0, dtb.as<int2>());
+            ae = impl == 1 ? launch_attention_tc2(&tq, &tkv, dspan.as<int32_t>(), ns, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0, dtb.as<int2>())
+                           : launch_attention_tc(&tq, &tkv, dspan.as<int32_t>(), ns, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0, dtb.as<int2>());
         }
         else if (impl == 1) ae = launch_attention_tc2(&tq, &tkv, dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0);
         else ae = launch_attention_tc(&tq, &tkv, dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0);
@@ -387,7 +388,7 @@ int32_t bertx_bench_attention(int32_t n_sent, int32_t len, int32_t n_head, int32
     const int impl = attn_impl_for(d_head);
     DevBuf dspan, dtb;
     int ns = 0;
-    if (impl == 1 && !getenv("BERT_ATTN_NOPACK")) {               // as the engine runs it: short sentences packed into spans
+    if (impl != 3 && !getenv("BERT_ATTN_NOPACK")) {               // as the engine runs it: short sentences packed into spans
         std::vector<int32_t> span(n_sent + 1);
         ns = pack_spans(cu.data(), n_sent, span.data());
         std::vector<int2> tb(T);
@@ -398,6 +399,7 @@ int32_t bertx_bench_attention(int32_t n_sent, int32_t len, int32_t n_head, int32
     }
     auto launch = [&]() {
         if (impl == 1 && ns > 0) return launch_attention_tc2(&tq, &tkv, dspan.as<int32_t>(), ns, len, n_head, d_head, o1.as<__half>(), W_Q4_0, prop.multiProcessorCount, 0, dtb.as<int2>());
+        if (impl == 0 && ns > 0) return launch_attention_tc(&tq, &tkv, dspan.as<int32_t>(), ns, len, n_head, d_head, o1.as<__half>(), W_Q4_0, prop.multiProcessorCount, 0, dtb.as<int2>());
         if (impl == 3) return launch_attention_tc3(&tq, &tkv, dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, prop.multiProcessorCount, 0);
         if (impl == 1) return launch_attention_tc2(&tq, &tkv, dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, prop.multiProcessorCount, 0);
         return launch_attention_tc(&tq, &tkv, dcu.as<int32_t>(), n_sent, len, n_head, d_head, o1.as<__half>(), W_Q4_0, prop.multiProcessorCount, 0);

@@ -48,7 +48,8 @@ constexpr uint32_t TM_COLS = 256;
 constexpr float kRescaleThreshold = 8.f;      // log2 units
 
 struct AttnTcParams {
-    const int32_t * cu;
+    const int32_t * cu;            // token offsets of the work units: sentences, or spans of several short sentences (pack_spans)
+    const int2 * tok_bounds;       // with spans: per token, [first, end) token of its own sentence (nullptr: units are sentences)
     __half * out;
     int n_sent, n_head, H, max_qt, fq_type;
     float scale_log2;
@@ -127,6 +128,9 @@ __device__ __forceinline__ float2 ex2_poly2(float2 x) {
 #endif
 #if BERT_ATTN_SPEC && !BERT_ATTN_MMASUM
 #error "BERT_ATTN_SPEC needs BERT_ATTN_MMASUM"
+#endif
+#if BERT_ATTN_SPEC
+#error "BERT_ATTN_SPEC predates the packed spans (per-row key bounds) and is no longer built"
 #endif
 #if !BERT_ATTN_MMASUM
 #error "the MMA issuer always forms the row sums (P x ones): BERT_ATTN_MMASUM=0 is no longer built"
@@ -292,6 +296,13 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
             const int len = it.len();
             const int nb = (len + AK - 1) / AK;
             float m_ref = -INFINITY, l = 0.f;
+            // keys this thread's query row may see, relative to the item's first token: the whole unit, or (packed spans,
+            // see attention_tc2.cu) the row's own sentence
+            int key_lo = 0, key_hi = len;
+            if (p.tok_bounds != nullptr) {
+                const int row = it.q0 + q * 32 + lane;
+                if (row < len) { const int2 bnd = __ldg(p.tok_bounds + it.t0 + row); key_lo = bnd.x - it.t0; key_hi = bnd.y - it.t0; }
+            }
             for (int b = 0; b < nb; ++b) {
                 const uint32_t gb = g + b;
                 mbar_wait(&s_full[gb & 1], (gb >> 1) & 1);
@@ -369,10 +380,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                 float s[64];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) { s[j] = __uint_as_float(r0[j]); s[32 + j] = __uint_as_float(r1[j]); }
-                const int kvalid = len - b * AK;           // keys of this block inside the sentence
-                if (kvalid < AK) {
+                const int klo = key_lo - b * AK, khi = key_hi - b * AK;     // this row's keys [klo, khi) of the block's 64
+                if (klo > 0 || khi < AK) {
 #pragma unroll
-                    for (int j = 0; j < 64; ++j) if (j >= kvalid) s[j] = -INFINITY;
+                    for (int j = 0; j < 64; ++j) if (j < klo || j >= khi) s[j] = -INFINITY;
                 }
                 float mx4[4] = {s[0], s[1], s[2], s[3]};      // four independent chains (a single one is latency-bound)
 #pragma unroll
@@ -380,12 +391,15 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
                     mx4[0] = fmaxf(mx4[0], s[j]); mx4[1] = fmaxf(mx4[1], s[j + 1]);
                     mx4[2] = fmaxf(mx4[2], s[j + 2]); mx4[3] = fmaxf(mx4[3], s[j + 3]);
                 }
-                const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * p.scale_log2;
+                // (a row whose sentence has no key in this block sees -inf only: the floor keeps its reference finite, its
+                // exponentials come out as 0 and nothing has to be rescaled until its first real block)
+                const float mx = fmaxf(fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * p.scale_log2, -1e30f);
                 // move the reference max only on the first block or when it is exceeded by > 2^8
                 const bool need = mx > m_ref + kRescaleThreshold;       // always true on the first block (m_ref = -inf)
+                const bool rescale = need && m_ref > -1e29f;            // the accumulator only holds something after a real block
                 float factor = 1.f;
                 if (need) { factor = ex2f(m_ref - mx); m_ref = mx; l *= factor; }   // (l unused with BERT_ATTN_MMASUM)
-                if (b >= 1 && __any_sync(0xffffffffu, need)) {
+                if (b >= 1 && __any_sync(0xffffffffu, rescale)) {
                     // rare: the previous block's P V must be in the accumulator before it may be rescaled.
                     // The wait is only paid here: S_b complete (s_full above) implies P V of block b-2 complete
                     // (issue order ..., PV_{b-2}, S_b, PV_{b-1}), so barrier (gb-1)&1 is at most one phase behind.
@@ -496,13 +510,13 @@ bool make_attention_tmaps(CUtensorMap * tm_q, CUtensorMap * tm_kv, const __half 
 
 cudaError_t launch_attention_tc(const CUtensorMap * tm_q, const CUtensorMap * tm_kv, const int32_t * cu_seqlens,
                                 int n_sent, int max_len, int n_head, int d_head, __half * out, int fq_type,
-                                int num_sms, cudaStream_t st) {
+                                int num_sms, cudaStream_t st, const int2 * tok_bounds) {
     if (n_sent <= 0) return cudaSuccess;
     if (d_head != AD || !tm_q || !tm_kv) return cudaErrorInvalidValue;
     cudaError_t e = cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmem);
     if (e != cudaSuccess) return e;
     AttnTcParams p;
-    p.cu = cu_seqlens; p.out = out; p.n_sent = n_sent; p.n_head = n_head; p.H = n_head * d_head;
+    p.cu = cu_seqlens; p.tok_bounds = tok_bounds; p.out = out; p.n_sent = n_sent; p.n_head = n_head; p.H = n_head * d_head;
     p.max_qt = (max_len + AQ - 1) / AQ; p.fq_type = fq_type;
     p.scale_log2 = 1.4426950408889634f / sqrtf((float) d_head);
     const long long total = (long long) n_sent * n_head * p.max_qt;

@@ -67,10 +67,10 @@ bool Engine::forward(Replica & r, const int32_t * d_ids, const int32_t * d_cu, i
         end();
     };
     begin(KK_EMBED);
-    // packed spans (head size 32 kernel): several short sentences share one attention work item; the embedding kernel
+    // packed spans: several short sentences share one attention work item; the embedding kernel
     // leaves every token's sentence bounds behind for the masks.  BERT_ATTN_PACK=0 turns it off (A/B).
     const int dh_ = H / hp.n_head;
-    const bool packed = n_spans > 0 && n_spans < n_sent && attn_pack && !attn_ref && !(dh_ == 64 && !attn_v2);
+    const bool packed = n_spans > 0 && n_spans < n_sent && attn_pack && !attn_ref && !(dh_ == 64 && attn_v3);
     L(KK_EMBED, launch_embed_ln(r.word, r.postype, r.ln_e_g, r.ln_e_b, d_ids, d_cu, n_sent, T, H,
                                 r.x, fq ? r.xq : nullptr, fq_type, packed ? r.tok_bounds : nullptr, st), "embed_ln");
     end();
@@ -90,6 +90,7 @@ bool Engine::forward(Replica & r, const int32_t * d_ids, const int32_t * d_cu, i
                 if (packed) ae = launch_attention_tc2(&r.ta_q, &r.ta_kv, d_cu + n_sent + 1, n_spans, max_len, hp.n_head, dh, r.ctx, fq_type, r.num_sms, st, r.tok_bounds);
                 else ae = launch_attention_tc2(&r.ta_q, &r.ta_kv, d_cu, n_sent, max_len, hp.n_head, dh, r.ctx, fq_type, r.num_sms, st);
             }
+            else if (packed) ae = launch_attention_tc(&r.ta_q, &r.ta_kv, d_cu + n_sent + 1, n_spans, max_len, hp.n_head, dh, r.ctx, fq_type, r.num_sms, st, r.tok_bounds);
             else ae = launch_attention_tc(&r.ta_q, &r.ta_kv, d_cu, n_sent, max_len, hp.n_head, dh, r.ctx, fq_type, r.num_sms, st);
             L(KK_ATTN, ae, "attention");
         }

@@ -92,7 +92,7 @@ cudaError_t launch_ln(const __half * x, const float * gamma, const float * beta,
 bool make_attention_tmaps(CUtensorMap * tm_q, CUtensorMap * tm_kv, const __half * qkv, uint64_t rows, int H);
 cudaError_t launch_attention_tc(const CUtensorMap * tm_q, const CUtensorMap * tm_kv, const int32_t * cu_seqlens,
                                 int n_sent, int max_len, int n_head, int d_head, __half * out, int fq_type,
-                                int num_sms, cudaStream_t st);
+                                int num_sms, cudaStream_t st, const int2 * tok_bounds = nullptr);
 // round-2 kernel (attention_tc2.cu): head sizes 64 and 32 (two heads per work item), eight softmax warps per CTA; same maps.
 // With tok_bounds (per token: [first, end) token of its sentence, written by launch_embed_ln) `cu_seqlens` may hold SPANS of
 // several whole sentences of at most 128 tokens in total (pack_spans): one work item then serves all of them, every query row
