@@ -38,7 +38,7 @@ WORKLOADS = {
     "tiny-q4_0-b64-s64": ("tiny-d64", "q4_0", 64, 64, "exact", "weak"),
 }
 DEFAULT_WORKLOAD = "bge-base-q4_0-b512-s512"
-NCU_GEMM_DRAM_BYTES_PER_LAUNCH = 960e6    # measured (ncu --set full, mean over the 4 GEMMs of a layer), see profiles/r1_head.md
+NCU_GEMM_DRAM_BYTES_PER_LAUNCH = 1.982e9   # measured (ncu --set full, mean over the 4 GEMMs of a layer at 262 144 tokens), see profiles/r2_rowwise_gemm_traffic.md
 
 
 def shard_range(n_items, rank, world):
@@ -316,7 +316,7 @@ def main():
                 "whole_forward_tflops": (job_gemm_flops + job_attn_flops) / (ms / args.steps / 1e3) / 1e12}
     if args.workload == DEFAULT_WORKLOAD:
         roofline["traffic"] = NCU_GEMM_DRAM_BYTES_PER_LAUNCH
-        roofline["traffic_note"] = "dram__bytes_read.sum + dram__bytes_write.sum, mean over the 4 GEMMs of a layer at 131072 tokens (profiles/r1_head.md)"
+        roofline["traffic_note"] = "dram__bytes_read.sum + dram__bytes_write.sum, mean over the 4 GEMMs of a layer at 262144 tokens per launch: 1.56 / 1.56 / 2.01 / 2.80 GB against algorithmic 1.61 / 1.61 / 2.01 / 2.82 GB (profiles/r2_rowwise_gemm_traffic.md)"
     # the HBM-bound row kernels against the measured copy bandwidth (algorithmic bytes)
     wbytes = {"f32": 4.0, "f16": 2.0, "q4_0": 18.0 / 32, "q4_1": 20.0 / 32}[ftype]
     twin = 2 if "q4" in ftype else 1

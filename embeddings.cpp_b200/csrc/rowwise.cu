@@ -6,6 +6,7 @@
 // One warp owns one row; lane l owns the 16-B chunks l + 32 i, so every warp access is a whole
 // 512-B line group; the q8 activation fake-quant (one scale per 32 values, ggml.c:1146-1300 /
 // 1425-1480) is a 4-lane shuffle.  Statistics are f32 warp-shuffle reductions.
+#include <cstdlib>
 #include "kernels.cuh"
 #include "ptx.cuh"
 
@@ -24,7 +25,8 @@ __device__ __forceinline__ float warp_sum(float v) {
 // Row LayerNorm + write-out shared by K0 and K3.  Lane l owns the 16-B chunks c = l + 32 i (8 fp16 each)
 // of the row, so every warp-level load/store is one fully coalesced 512-B access; a q8 block (32 values)
 // is 4 adjacent lanes.  `v` holds the row (0 in chunks past the row end), `s` this lane's sum.
-template <int NCH>
+// FULL: the row is exactly NCH * 32 chunks (H = 256 NCH), so no chunk needs a bounds predicate.
+template <int NCH, bool FULL = false>
 __device__ __forceinline__ void ln_row_finish(float (&v)[NCH][8], float s, int lane, int H,
                                               const float * __restrict__ gamma, const float * __restrict__ beta,
                                               __half * __restrict__ out_row, __half * __restrict__ out_fq_row, int fq_type) {
@@ -33,7 +35,7 @@ __device__ __forceinline__ void ln_row_finish(float (&v)[NCH][8], float s, int l
     float s2 = 0.f;
 #pragma unroll
     for (int i = 0; i < NCH; ++i) {
-        if (lane + 32 * i < nchunk) {
+        if (FULL || lane + 32 * i < nchunk) {
 #pragma unroll
             for (int e = 0; e < 8; ++e) { v[i][e] -= mean; s2 += v[i][e] * v[i][e]; }
         }
@@ -45,7 +47,7 @@ __device__ __forceinline__ void ln_row_finish(float (&v)[NCH][8], float s, int l
 #pragma unroll
     for (int i = 0; i < NCH; ++i) {
         const int c = lane + 32 * i;
-        const bool ok = c < nchunk;
+        const bool ok = FULL || c < nchunk;
         if (ok) {
             const float4 g0 = __ldg(reinterpret_cast<const float4 *>(gamma) + 2 * c);
             const float4 g1 = __ldg(reinterpret_cast<const float4 *>(gamma) + 2 * c + 1);
@@ -121,7 +123,7 @@ ln_kernel(const __half * __restrict__ x, const float * __restrict__ gamma, const
 // Same chunk ownership as K3: lane l takes the 8-value chunks l + 32 i, i.e. for a q4 table 8 of a block's
 // 16 payload bytes (file nibble order: byte j = e[j] | e[j+16] << 4) and the block's scale.  The position of
 // a packed token inside its sentence comes from a warp-cooperative 32-way search over cu_seqlens.
-template <int NCH>
+template <int NCH, int WT, bool FULL>
 __global__ void __launch_bounds__(ROWS_PER_CTA * 32)
 embed_ln_kernel(const DevTable word, const float * __restrict__ postype,
                 const float * __restrict__ gamma, const float * __restrict__ beta,
@@ -133,40 +135,10 @@ embed_ln_kernel(const DevTable word, const float * __restrict__ postype,
     if (row >= T) return;
     const int lane = threadIdx.x & 31;
     const int nchunk = H / 8, nb = H / 32;
+    // Load order = dependency depth: the token id and the sentence search (cu_seqlens is small and cache-resident) go first and
+    // overlap; then the word row (needs the id) and the position row (needs the sentence start) are requested together, and
+    // nothing is consumed before every request of the row is in flight -- one DRAM round trip per row instead of one per stage.
     int id = __ldg(ids + row);
-    if (id < 0 || id >= word.rows) id = 0;                  // never read out of the table
-    float v[NCH][8];
-#pragma unroll
-    for (int i = 0; i < NCH; ++i) {
-        const int c = lane + 32 * i;
-#pragma unroll
-        for (int e = 0; e < 8; ++e) v[i][e] = 0.f;
-        if (c >= nchunk) continue;
-        if (word.type == W_F32) {
-            const float4 * q = reinterpret_cast<const float4 *>(reinterpret_cast<const float *>(word.data) + (size_t) id * H) + 2 * c;
-            const float4 f0 = __ldg(q), f1 = __ldg(q + 1);
-            v[i][0] = f0.x; v[i][1] = f0.y; v[i][2] = f0.z; v[i][3] = f0.w;
-            v[i][4] = f1.x; v[i][5] = f1.y; v[i][6] = f1.z; v[i][7] = f1.w;
-        } else if (word.type == W_F16) {
-            const uint4 u = __ldg(reinterpret_cast<const uint4 *>(reinterpret_cast<const __half *>(word.data) + (size_t) id * H) + c);
-            const __half2 * h = reinterpret_cast<const __half2 *>(&u);
-#pragma unroll
-            for (int e = 0; e < 4; ++e) { const float2 f = __half22float2(h[e]); v[i][2 * e] = f.x; v[i][2 * e + 1] = f.y; }
-        } else {
-            const size_t blk = (size_t) id * nb + (c >> 2);
-            const int k = c & 3;                             // values 8k .. 8k+7 of the block
-            const uint2 u = __ldg(reinterpret_cast<const uint2 *>(word.data) + blk * 2 + (k & 1));
-            const int sh = (k >> 1) * 4;
-            const float d = __half2float(__ldg(word.qd + blk));
-            const float m = word.type == W_Q4_1 ? __half2float(__ldg(word.qm + blk)) : 0.f;
-            const uint32_t w[2] = {u.x, u.y};
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const int qv = (int) ((w[j >> 2] >> (8 * (j & 3) + sh)) & 15u);
-                v[i][j] = word.type == W_Q4_0 ? (float) (qv - 8) * d : (float) qv * d + m;
-            }
-        }
-    }
     // sentence of this packed token: largest s with cu[s] <= row, 32 pivots per round
     int lo = 0, hi = n_sent;
     while (hi - lo > 1) {
@@ -183,20 +155,74 @@ embed_ln_kernel(const DevTable word, const float * __restrict__ postype,
     // by-product for the attention kernel that packs several short sentences into one work item: [first, end) token of this
     // token's sentence
     if (tok_bounds != nullptr && lane == 0) tok_bounds[row] = make_int2(sent_t0, __ldg(cu + lo + 1));
+    if (id < 0 || id >= word.rows) id = 0;                  // never read out of the table
+    float v[NCH][8];
+    float4 p0[NCH], p1[NCH];                                // position + token-type row
+    uint4 raw[NCH];                                         // word row as stored (f32: first half; see below)
+    float4 raw2[WT == W_F32 ? NCH : 1];                     // f32 table: second half of the chunk
+    __half qd[NCH], qm[NCH];
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+        const int c = lane + 32 * i;
+        if (!FULL) {
+            raw[i] = make_uint4(0u, 0u, 0u, 0u);
+            p0[i] = p1[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        qd[i] = qm[i] = __ushort_as_half(0);
+        if (!FULL && c >= nchunk) continue;
+        const float4 * q = reinterpret_cast<const float4 *>(postype + (size_t) pos * H) + 2 * c;
+        p0[i] = __ldg(q); p1[i] = __ldg(q + 1);
+        if (WT == W_F32) {
+            const float4 * w = reinterpret_cast<const float4 *>(reinterpret_cast<const float *>(word.data) + (size_t) id * H) + 2 * c;
+            const float4 f0 = __ldg(w);
+            raw[i] = make_uint4(__float_as_uint(f0.x), __float_as_uint(f0.y), __float_as_uint(f0.z), __float_as_uint(f0.w));
+            raw2[WT == W_F32 ? i : 0] = __ldg(w + 1);
+        } else if (WT == W_F16) {
+            raw[i] = __ldg(reinterpret_cast<const uint4 *>(reinterpret_cast<const __half *>(word.data) + (size_t) id * H) + c);
+        } else {
+            const size_t blk = (size_t) id * nb + (c >> 2);
+            const uint2 u = __ldg(reinterpret_cast<const uint2 *>(word.data) + blk * 2 + (c & 1));
+            raw[i].x = u.x; raw[i].y = u.y;
+            qd[i] = __ldg(word.qd + blk);
+            if (WT == W_Q4_1) qm[i] = __ldg(word.qm + blk);
+        }
+    }
     float s = 0.f;
 #pragma unroll
     for (int i = 0; i < NCH; ++i) {
         const int c = lane + 32 * i;
-        if (c < nchunk) {
-            const float4 * q = reinterpret_cast<const float4 *>(postype + (size_t) pos * H) + 2 * c;
-            const float4 f0 = __ldg(q), f1 = __ldg(q + 1);
-            v[i][0] += f0.x; v[i][1] += f0.y; v[i][2] += f0.z; v[i][3] += f0.w;
-            v[i][4] += f1.x; v[i][5] += f1.y; v[i][6] += f1.z; v[i][7] += f1.w;
+        if (!FULL) {
 #pragma unroll
-            for (int e = 0; e < 8; ++e) s += v[i][e];
+            for (int e = 0; e < 8; ++e) v[i][e] = 0.f;
+            if (c >= nchunk) continue;
         }
+        if (WT == W_F32) {
+            v[i][0] = __uint_as_float(raw[i].x); v[i][1] = __uint_as_float(raw[i].y);
+            v[i][2] = __uint_as_float(raw[i].z); v[i][3] = __uint_as_float(raw[i].w);
+            const float4 r2 = raw2[WT == W_F32 ? i : 0];
+            v[i][4] = r2.x; v[i][5] = r2.y; v[i][6] = r2.z; v[i][7] = r2.w;
+        } else if (WT == W_F16) {
+            const __half2 * h = reinterpret_cast<const __half2 *>(&raw[i]);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) { const float2 f = __half22float2(h[e]); v[i][2 * e] = f.x; v[i][2 * e + 1] = f.y; }
+        } else {
+            const int sh = ((c & 3) >> 1) * 4;               // values 8k .. 8k+7 of the block, k = c & 3
+            const float d = __half2float(qd[i]);
+            const float m = __half2float(qm[i]);
+            // nibble -> float without an int-to-float conversion: OR it into the mantissa of 2^23 (exact, same value as the cast)
+            const uint32_t w[2] = {raw[i].x >> sh, raw[i].y >> sh};
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float f = __uint_as_float(((w[j >> 2] >> (8 * (j & 3))) & 15u) | 0x4B000000u);
+                v[i][j] = WT == W_Q4_0 ? (f - 8388616.f) * d : (f - 8388608.f) * d + m;
+            }
+        }
+        v[i][0] += p0[i].x; v[i][1] += p0[i].y; v[i][2] += p0[i].z; v[i][3] += p0[i].w;
+        v[i][4] += p1[i].x; v[i][5] += p1[i].y; v[i][6] += p1[i].z; v[i][7] += p1[i].w;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) s += v[i][e];
     }
-    ln_row_finish<NCH>(v, s, lane, H, gamma, beta, out + (size_t) row * H, out_fq ? out_fq + (size_t) row * H : nullptr, fq_type);
+    ln_row_finish<NCH, FULL>(v, s, lane, H, gamma, beta, out + (size_t) row * H, out_fq ? out_fq + (size_t) row * H : nullptr, fq_type);
 }
 
 // one CTA per sentence; thread = (8-column chunk, token stripe).  1024 threads keep enough 16-B loads in
@@ -262,12 +288,18 @@ cudaError_t launch_embed_ln(const DevTable & word, const float * postype, const 
     if (T <= 0) return cudaSuccess;
     const int grid = (T + ROWS_PER_CTA - 1) / ROWS_PER_CTA;
     const int nch = (H / 8 + 31) / 32;
-#define EMBED_LAUNCH(NCH_) launch_pdl(embed_ln_kernel<NCH_>, dim3(grid), dim3(ROWS_PER_CTA * 32), 0, st, \
+    const bool full = (H / 8) == 32 * nch;
+#define EMBED_LAUNCH3(NCH_, WT_, FULL_) launch_pdl(embed_ln_kernel<NCH_, WT_, FULL_>, dim3(grid), dim3(ROWS_PER_CTA * 32), 0, st, \
         word, postype, gamma, beta, ids, cu_seqlens, n_sent, T, H, out, out_fq, fq_type, tok_bounds)
+#define EMBED_LAUNCH2(NCH_, WT_) (full ? EMBED_LAUNCH3(NCH_, WT_, true) : EMBED_LAUNCH3(NCH_, WT_, false))
+#define EMBED_LAUNCH(NCH_) (word.type == W_F32 ? EMBED_LAUNCH2(NCH_, W_F32) : word.type == W_F16 ? EMBED_LAUNCH2(NCH_, W_F16) : \
+                            word.type == W_Q4_0 ? EMBED_LAUNCH2(NCH_, W_Q4_0) : EMBED_LAUNCH2(NCH_, W_Q4_1))
     if (nch <= 1) return EMBED_LAUNCH(1);
     if (nch == 2) return EMBED_LAUNCH(2);
     if (nch == 3) return EMBED_LAUNCH(3);
     return EMBED_LAUNCH(4);
+#undef EMBED_LAUNCH3
+#undef EMBED_LAUNCH2
 #undef EMBED_LAUNCH
 }
 
