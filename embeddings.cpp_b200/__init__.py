@@ -75,6 +75,8 @@ def lib():
     L.bertx_kernel_launches.argtypes = [vp]
     L.bertx_plan.restype = c_i32
     L.bertx_plan.argtypes = [vp, c_i32, c_i32, pi, pi, pi, c_i32]
+    L.bertx_pack_spans.restype = c_i32
+    L.bertx_pack_spans.argtypes = [c_i32, pi, pi]
     L.bertx_tokenize_batch.restype = c_i64
     L.bertx_tokenize_batch.argtypes = [vp, c_i32, c_i32, ctypes.POINTER(cp), pi, c_i64, pi]
     L.bertx_stage.restype = c_i32
@@ -278,6 +280,17 @@ class BertModel:
             raise RuntimeError(f"bertx_profile_staged failed ({rc})")
         names = ["embed_ln", "gemm", "attention", "add_ln", "pool_norm", "other"]
         return {n: (float(ms[i]), int(cnt[i])) for i, n in enumerate(names)}
+
+
+def pack_spans(lens):
+    """Attention work units of one micro-batch (bertx_pack_spans, host only): token offsets of the spans that consecutive
+    sentences of these token counts are grouped into (at most 128 tokens per span; a longer sentence is its own span)."""
+    lens = np.ascontiguousarray(lens, dtype=np.int32)
+    span = np.zeros(len(lens) + 1, dtype=np.int32)
+    n = lib().bertx_pack_spans(len(lens), _ip(lens), _ip(span))
+    if n < 0:
+        raise RuntimeError(f"bertx_pack_spans failed ({n})")
+    return span[:n + 1].copy()
 
 
 def convert_safetensors(model_dir, fname_out, ftype):

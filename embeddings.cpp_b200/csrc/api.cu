@@ -216,6 +216,13 @@ int32_t bertx_plan(struct bert_ctx * ctx, int32_t n_devices, int32_t n_sent, con
     }
 }
 
+int32_t bertx_pack_spans(int32_t n_sent, const int32_t * n_tokens, int32_t * span_cu) {
+    if (n_sent < 0 || (n_sent > 0 && (!n_tokens || !span_cu))) return -1;
+    std::vector<int32_t> cu((size_t) n_sent + 1, 0);
+    for (int i = 0; i < n_sent; ++i) cu[i + 1] = cu[i] + n_tokens[i];
+    return b200::pack_spans(cu.data(), n_sent, span_cu);
+}
+
 int32_t bertx_set_pooling(struct bert_ctx * ctx, int32_t mode) {
     if (!ctx || (mode != 0 && mode != 1)) return -1;
     std::lock_guard<std::mutex> lk(ctx->eng.mu);

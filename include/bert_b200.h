@@ -40,6 +40,13 @@ BERT_API int64_t bertx_tokenize_batch(struct bert_ctx * ctx, int32_t n_threads, 
 BERT_API int32_t bertx_plan(struct bert_ctx * ctx, int32_t n_devices, int32_t n_sent, const int32_t * n_tokens,
                             int32_t * mb_of_sentence, int32_t * mb_tokens, int32_t cap);
 
+/* The attention work units of one micro-batch (host only, no context needed): consecutive sentences whose token counts
+ * n_tokens[0..n_sent) add up to at most 128 share a span, a longer sentence is a span of its own (the packed spans of
+ * attention_tc.cu / attention_tc2.cu; no counterpart in the reference, whose ggml_soft_max pads every sentence to the
+ * batch maximum, bert.cpp:1018-1036).  Writes the span boundaries as token offsets, span_cu[0..n_spans], capacity
+ * n_sent + 1; returns n_spans. */
+BERT_API int32_t bertx_pack_spans(int32_t n_sent, const int32_t * n_tokens, int32_t * span_cu);
+
 /* Stage a whole job on device `dev` (index into the context's device list): packed ids
  * + lengths are copied to HBM and cut into micro-batches.  Returns 0 on success. */
 BERT_API int32_t bertx_stage(struct bert_ctx * ctx, int32_t dev, int32_t n_sent,

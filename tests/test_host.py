@@ -271,3 +271,29 @@ def test_text_pointer_table_round_trips(pkg):
         for i, t in enumerate(texts):
             want = t if isinstance(t, bytes) else t.encode("utf-8")
             assert p[i] == want.split(b"\0")[0]
+
+
+def test_span_packing_matches_its_definition(pkg):
+    """bertx_pack_spans (the host half of the packed attention spans): greedy, in order, spans of several sentences hold at most
+    128 tokens, a longer sentence stays alone, every sentence is in exactly one span -- against a direct Python restatement."""
+    def restate(lens):
+        cu = np.concatenate([[0], np.cumsum(lens)])
+        out, s = [0], 0
+        while s < len(lens):
+            e = s + 1
+            while e < len(lens) and cu[e + 1] - cu[s] <= 128:
+                e += 1
+            out.append(int(cu[e])); s = e
+        return np.array(out, dtype=np.int32)
+    rng = np.random.default_rng(5)
+    cases = [[], [1], [128], [129], [64, 64], [64, 65], [127, 1, 1], [512, 3, 3, 500, 2], [1] * 300,
+             list(rng.integers(1, 40, 500)), list(rng.integers(1, 513, 200)), list(rng.integers(100, 140, 50))]
+    for lens in cases:
+        got = pkg.pack_spans(lens)
+        assert np.array_equal(got, restate(lens)), lens[:10]
+        cu = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+        assert got[0] == 0 and got[-1] == cu[-1] and np.all(np.diff(got) > 0) or len(lens) == 0
+        assert np.isin(got, cu).all()                                   # spans end on sentence boundaries
+        for a, b in zip(got[:-1], got[1:]):                             # > 128 tokens only if it is one sentence
+            if b - a > 128:
+                assert np.searchsorted(cu, b) - np.searchsorted(cu, a) == 1
