@@ -47,6 +47,15 @@ constexpr int kSmemLimit = 232448;                   // 227 KB opt-in limit per 
 #ifndef BERT_DQ_SYNC
 #define BERT_DQ_SYNC 0
 #endif
+//   BERT_LN_RES2       0 (default) fused-LayerNorm epilogue: a warp's second residual box is requested into the residual buffer once
+//                      the first has been read out of it; 1: it travels into the warp's output staging buffer (idle until
+//                      pass 2) from the top of the tile.  The wait this removes was 10.6 % of the epilogue warps' samples in
+//                      the attention-output GEMM, yet the kernel is no faster (0.4513 vs 0.4483 ms at 262 144 x 768 x 768,
+//                      1.0994 vs 1.0917 ms at K = 3072, two alternations): the time moves to the statistics exchange
+//                      (profiles/r2_rowwise_gemm_traffic.md)
+#ifndef BERT_LN_RES2
+#define BERT_LN_RES2 0
+#endif
 template <int BN, int WT, bool LN, bool RES, bool EPB = false> struct GemmCfg {
     static constexpr bool kQ4      = WT != W_F16;
     static constexpr int kBHalf    = BN / 2;                 // B rows this CTA supplies
@@ -86,7 +95,7 @@ template <int BN, int WT, bool LN, bool RES, bool EPB = false> struct GemmCfg {
     static constexpr int kSN       = kQ4 ? 6 : 0;
     static constexpr int kSmemBytes = kSA * kABytes + kSB * kBBytes + kSN * kNibSlot + kFixed;
     static_assert(kSmemBytes <= kSmemLimit, "shared memory budget");
-    static_assert(2 * kSA + 2 * kSB + 2 * kSN + 14 <= (kBarBytes - 8) / 8, "barrier region");
+    static_assert(2 * kSA + 2 * kSB + 2 * kSN + 22 <= (kBarBytes - 8) / 8, "barrier region");
 };
 
 struct GemmParams {
@@ -264,7 +273,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     uint64_t * tempty = tfull + 2;              // [2]   leader's copy is live: 16 epilogue warps arrive
     uint64_t * rfull = tempty + 2;              // [8] residual box, per epilogue warp
     uint64_t * ln_bar = rfull + 8;              // [2] LN: partial statistics of all pairs have landed (by tile parity)
-    uint32_t * tmem_slot = (uint32_t *) (ln_bar + 2);
+    uint64_t * rfull2 = ln_bar + 2;             // [8] LN, 256-wide tiles: the warp's second residual box (lands in its output staging)
+    uint32_t * tmem_slot = (uint32_t *) (rfull2 + 8);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t crank = cluster_ctarank();                 // rank in the cluster
@@ -292,7 +302,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             for (int s = 0; s < SN; ++s) { mbar_init(&n_full[s], 1); mbar_init(&n_empty[s], DQ_GROUP_WARPS); }
         }
         for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 2 * EPI_WARPS); }
-        for (int i = 0; i < 8; ++i) mbar_init(&rfull[i], 1);
+        for (int i = 0; i < 8; ++i) { mbar_init(&rfull[i], 1); mbar_init(&rfull2[i], 1); }
         if (LN) { mbar_init(&ln_bar[0], 1); mbar_init(&ln_bar[1], 1); }
         fence_mbar_init();
     }
@@ -424,11 +434,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         };
         if (my_tiles > 0 && lane == 0) res_load(0);
         uint32_t rph = 0;                          // residual barrier phase
+        constexpr bool RES2 = BERT_LN_RES2 != 0 && NBW == 2;
+        uint64_t * rbar2 = rfull2 + e;
+        uint32_t rph2 = 0;
         for (int it = 0; it < my_tiles; ++it) {
             const int acc = it & 1;
             const uint32_t acc_ph = (it >> 1) & 1;
             int mb, nb; tw.get(it, mb, nb);
             const int wrow0 = mb * (2 * BM) + (int) rank * BM + q * 32;
+            if (RES2 && lane == 0) {
+                // the second residual box of this tile -> the output staging buffer, which pass 1 does not use (the previous
+                // tile's stores must have finished reading it); it travels while the accumulator and the first box are waited for
+                tma_store_wait_read<0>();
+                mbar_expect_tx(rbar2, 4096);
+                tma_load_2d(st, &tmap_res, rbar2, nb * BN + (half + 2) * 64, wrow0);
+            }
             wait_tfull(&tfull[acc], acc_ph);
             tc_fence_after_sync();
             uint32_t hv[NBW][32];                  // pre-LN values as fp16 pairs
@@ -436,18 +456,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             for (int bi = 0; bi < NBW; ++bi) {
                 const int b = half + 2 * bi;
                 uint4 rr[8];
-                mbar_wait(rbar, rph); rph ^= 1;
+                const uint8_t * rsrc = (RES2 && bi == 1) ? st : rs;
+                if (RES2 && bi == 1) { mbar_wait(rbar2, rph2); rph2 ^= 1; }
+                else { mbar_wait(rbar, rph); rph ^= 1; }
 #pragma unroll
-                for (int c = 0; c < 8; ++c) rr[c] = *reinterpret_cast<const uint4 *>(rs + lane * 128 + ((c ^ (lane & 7)) << 4));
+                for (int c = 0; c < 8; ++c) rr[c] = *reinterpret_cast<const uint4 *>(rsrc + lane * 128 + ((c ^ (lane & 7)) << 4));
                 fence_loads_done();                           // before the buffer goes back to the TMA (see the plain epilogue)
                 __syncwarp();
-                if (bi + 1 < NBW && lane == 0) {              // this tile's next box
+                if (!RES2 && bi + 1 < NBW && lane == 0) {     // this tile's next box
                     mbar_expect_tx(rbar, 4096);
                     tma_load_2d(rs, &tmap_res, rbar, nb * BN + (b + 2) * 64, wrow0);
                 }
                 // EPB: the residual buffer is not the twin's staging, so the next tile's first box can travel
-                // while this tile is normalised and stored
-                if (EPB && bi + 1 == NBW && it + 1 < my_tiles && lane == 0) res_load(it + 1);
+                // while this tile is normalised and stored (RES2: as soon as this tile's first box has been read out)
+                if (EPB && bi + 1 == (RES2 ? 1 : NBW) && it + 1 < my_tiles && lane == 0) res_load(it + 1);
 #pragma unroll
                 for (int hh = 0; hh < 2; ++hh) {
                     uint32_t r[32];
