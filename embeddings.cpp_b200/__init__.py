@@ -186,13 +186,17 @@ class BertModel:
 
     # -- reference surface -----------------------------------------------------------
     def encode(self, sentences, batch_size=16):
-        """bert_encode_batch; returns [n, n_embd] float32 (sample_dylib.py:42-62)."""
+        """bert_encode_batch; returns [n, n_embd] float32 -- or, like the reference's binding, one [n_embd] vector when
+        `sentences` is a single string (sample_dylib.py:42-62)."""
+        single = isinstance(sentences, (str, bytes))
+        if single:
+            sentences = [sentences]
         n = len(sentences)
         out = np.zeros((n, self.n_embd), dtype=np.float32)
         if n == 0:
             return out
         self.lib.bert_encode_batch(self.ctx, self.n_threads, batch_size, n, _text_ptrs(sentences), _row_ptrs(out))
-        return out
+        return out[0] if single else out
 
     def tokenize(self, text, n_max=None):
         n_max = self.n_max_tokens if n_max is None else n_max

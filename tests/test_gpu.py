@@ -155,6 +155,9 @@ def test_edge_cases_and_error_conventions(models, ft, capfd):
     cos, err = cos_and_maxabs(got, want)
     assert cos >= COS_MIN and err <= MAX_ABS[ft], (cos, err)
     assert np.allclose(np.linalg.norm(got, axis=1), 1.0, atol=1e-4)
+    # a single string instead of a list: one vector, as the reference's Python binding returns (sample_dylib.py:42-62)
+    one = m.encode("hello world !")
+    assert one.shape == (got.shape[1],) and np.array_equal(one, m.encode([b"hello world !"])[0])
     # too many tokens: message on stderr, outputs untouched (reference bert.cpp:867-871)
     before = m.kernel_launches()
     out = m.forward_tokens([[101] + [200] * 600 + [102], [101, 102]])
