@@ -73,3 +73,26 @@ def test_loading_the_checkpoint_directly_equals_loading_the_converted_file(tmp_p
     b.close()
     assert np.array_equal(got, want)                       # same bytes on the device, same kernels: bit-identical
     assert np.all(np.isfinite(got)) and np.allclose(np.linalg.norm(got, axis=1), 1.0, atol=1e-3)
+
+
+def test_convert_tool_has_the_reference_scripts_command_line(tmp_path):
+    """examples/convert_b200: `dir-model [ftype]` -> dir-model/ggml-model-{f32,f16}.bin with the script's bytes, default f16,
+    usage text and exit code 1 without arguments, 'Invalid ftype' for a bad type (convert-to-ggml.py:10-51)."""
+    import shutil
+    import subprocess
+    ge.load_package()                                                     # builds libbert.so if needed
+    assert subprocess.run(["make", "-C", os.path.join(ROOT, "examples"), "bin/convert_b200"], capture_output=True).returncode == 0
+    tool = os.path.join(ROOT, "examples", "bin", "convert_b200")
+    ckpt = tmp_path / "ckpt"
+    shutil.copytree(HF, ckpt)
+    r = subprocess.run([tool], capture_output=True, text=True)
+    assert r.returncode == 1 and "Usage" in r.stderr
+    r = subprocess.run([tool, str(ckpt), "9"], capture_output=True, text=True)
+    assert r.returncode == 1 and "Invalid ftype" in r.stderr
+    for args, name in (([str(ckpt), "0"], "f32"), ([str(ckpt)], "f16")):
+        r = subprocess.run([tool] + args, capture_output=True, text=True)
+        out = ckpt / f"ggml-model-{name}.bin"
+        assert r.returncode == 0 and f"Done. Output file: {out}" in r.stdout, r.stderr
+        assert _sha(str(out)) == EXPECTED["sha256"][name]
+    r = subprocess.run([tool, str(tmp_path / "missing")], capture_output=True, text=True)
+    assert r.returncode == 1
