@@ -93,6 +93,8 @@ def lib():
     L.bertx_bench_attention.argtypes = [c_i32, c_i32, c_i32, c_i32, c_i32, pf]
     L.bertx_selftest_attention.restype = c_i32
     L.bertx_selftest_attention.argtypes = [c_i32, c_i32, c_i32, c_i32, c_i32, pf, pf]
+    L.bertx_debug_attention.restype = c_i32
+    L.bertx_debug_attention.argtypes = [c_i32, pi, c_i32, c_i32, c_i32, c_i32, vp, vp]
     L.bertx_quantize_file.restype = c_i32
     L.bertx_quantize_file.argtypes = [cp, cp, c_i32]
     L.bertx_quantize_rows_noalloc.restype = c_i32
@@ -335,6 +337,18 @@ def selftest_attention(n_sent, max_len, n_head, d_head, seed=0):
     err, ref = ctypes.c_float(0), ctypes.c_float(0)
     rc = lib().bertx_selftest_attention(n_sent, max_len, n_head, d_head, seed, ctypes.byref(err), ctypes.byref(ref))
     return rc, err.value, ref.value
+
+
+def debug_attention(lens, n_head, d_head, seed=0, flags=0):
+    """bertx_debug_attention: (qkv [T, 3, H] float16, out [T, H] float16) of the production attention kernel on random inputs."""
+    lens = np.ascontiguousarray(lens, dtype=np.int32)
+    T, H = int(lens.sum()), n_head * d_head
+    qkv = np.zeros((T, 3, H), dtype=np.float16)
+    out = np.zeros((T, H), dtype=np.float16)
+    rc = lib().bertx_debug_attention(len(lens), _ip(lens), n_head, d_head, seed, flags, qkv.ctypes.data, out.ctypes.data)
+    if rc != 0:
+        raise RuntimeError(f"bertx_debug_attention failed ({rc})")
+    return qkv, out
 
 
 def bench_attention(n_sent, length, n_head, d_head, reps=10):

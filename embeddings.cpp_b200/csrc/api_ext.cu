@@ -361,6 +361,60 @@ int32_t bertx_selftest_attention(int32_t n_sent, int32_t max_len, int32_t n_head
     return compare_h(o1.as<__half>(), o2.as<__half>(), T * H, max_abs_err, max_ref) ? 0 : -8;
 }
 
+// Debug aid for a per-kernel check against numpy (tests/test_gpu.py::test_attention_against_numpy): the production attention
+// kernel on random fp16 q/k/v for sentences of the given lengths; the inputs ([T][3H] fp16 bits) and the kernel's output
+// ([T][H] fp16 bits) are copied to the caller's arrays.  flags: the seed bits of bertx_selftest_attention (kernel choice, bit 14
+// = no span packing).
+int32_t bertx_debug_attention(int32_t n_sent, const int32_t * lens, int32_t n_head, int32_t d_head, int32_t seed, int32_t flags,
+                              uint16_t * qkv_out, uint16_t * out) {
+    if (n_sent <= 0 || !lens || !qkv_out || !out || (d_head != 32 && d_head != 64)) return -1;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { fprintf(stderr, "bertx_debug_attention: no CUDA device\n"); return -2; }
+    std::mt19937 rng((uint32_t) seed);
+    std::normal_distribution<float> nd(0.f, 1.f);
+    const int H = n_head * d_head;
+    std::vector<int32_t> cu(n_sent + 1, 0);
+    int max_len = 0;
+    for (int i = 0; i < n_sent; ++i) {
+        if (lens[i] <= 0) return -1;
+        cu[i + 1] = cu[i] + lens[i];
+        max_len = std::max(max_len, (int) lens[i]);
+    }
+    const size_t T = (size_t) cu[n_sent];
+    std::vector<uint16_t> hq(T * 3 * H);
+    for (auto & v : hq) v = f2h_bits(1.5f * nd(rng));
+    DevBuf qkv, dcu, o1, dspan, dtb;
+    if (!qkv.alloc(hq.size() * 2) || !dcu.alloc(cu.size() * 4) || !o1.alloc(T * H * 2)) return -3;
+    cudaMemcpy(qkv.p, hq.data(), hq.size() * 2, cudaMemcpyHostToDevice);
+    cudaMemcpy(dcu.p, cu.data(), cu.size() * 4, cudaMemcpyHostToDevice);
+    cudaMemset(o1.p, 0xFF, T * H * 2);
+    CUtensorMap tq, tkv;
+    cudaDeviceProp prop; cudaGetDeviceProperties(&prop, 0);
+    if (!make_attention_tmaps(&tq, &tkv, qkv.as<__half>(), T, H)) return -4;
+    const int impl = d_head != 64 ? 1 : (flags & 2048) ? 0 : (flags & 4096) ? 1 : (flags & 8192) ? 3 : attn_impl_for(d_head);
+    cudaError_t ae;
+    if (impl == 3) {
+        ae = launch_attention_tc3(&tq, &tkv, dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0);
+    } else if (!(flags & 16384)) {
+        std::vector<int32_t> span(n_sent + 1);
+        const int ns = pack_spans(cu.data(), n_sent, span.data());
+        std::vector<int2> tb(T);
+        for (int i = 0; i < n_sent; ++i) for (int t = cu[i]; t < cu[i + 1]; ++t) tb[t] = make_int2(cu[i], cu[i + 1]);
+        if (!dspan.alloc(span.size() * 4) || !dtb.alloc(tb.size() * 8)) return -3;
+        cudaMemcpy(dspan.p, span.data(), (size_t) (ns + 1) * 4, cudaMemcpyHostToDevice);
+        cudaMemcpy(dtb.p, tb.data(), tb.size() * 8, cudaMemcpyHostToDevice);
+        ae = impl == 1 ? launch_attention_tc2(&tq, &tkv, dspan.as<int32_t>(), ns, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0, dtb.as<int2>())
+                       : launch_attention_tc(&tq, &tkv, dspan.as<int32_t>(), ns, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0, dtb.as<int2>());
+    } else {
+        ae = impl == 1 ? launch_attention_tc2(&tq, &tkv, dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0)
+                       : launch_attention_tc(&tq, &tkv, dcu.as<int32_t>(), n_sent, max_len, n_head, d_head, o1.as<__half>(), -1, prop.multiProcessorCount, 0);
+    }
+    if (!cuda_ok(ae, "debug attention launch") || !cuda_ok(cudaDeviceSynchronize(), "debug attention")) return -6;
+    memcpy(qkv_out, hq.data(), hq.size() * 2);
+    if (!cuda_ok(cudaMemcpy(out, o1.p, T * H * 2, cudaMemcpyDeviceToHost), "debug attention copy")) return -6;
+    return 0;
+}
+
 int32_t bertx_bench_attention(int32_t n_sent, int32_t len, int32_t n_head, int32_t d_head, int32_t reps, float * ms_total) {
     if (n_sent <= 0 || len <= 0 || reps <= 0 || (d_head != 32 && d_head != 64)) return -1;
     int ndev = 0;

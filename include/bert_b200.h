@@ -86,6 +86,14 @@ BERT_API int32_t bertx_bench_gemm(int32_t M, int32_t N, int32_t K, int32_t wtype
 BERT_API int32_t bertx_selftest_attention(int32_t n_sent, int32_t max_len, int32_t n_head, int32_t d_head,
                                           int32_t seed, float * max_abs_err, float * max_ref);
 
+/* Debug aid for a per-kernel check against an independent implementation: the production attention kernel on seeded random
+ * fp16 q / k / v for sentences of lens[0..n_sent) tokens (flags: the kernel-choice bits of bertx_selftest_attention's seed);
+ * the inputs ([T][3 n_head d_head] fp16 bit patterns, q | k | v per token as the QKV GEMM writes them) and the kernel's
+ * output ([T][n_head d_head] fp16 bit patterns) are copied to the caller's host arrays.  Replaces nothing in the reference;
+ * the arithmetic checked is bert.cpp:1018-1036 (scale, masked soft-max, weighted sum of V) per sentence and head. */
+BERT_API int32_t bertx_debug_attention(int32_t n_sent, const int32_t * lens, int32_t n_head, int32_t d_head, int32_t seed,
+                                       int32_t flags, uint16_t * qkv_out, uint16_t * out);
+
 /* Time `reps` back-to-back launches of the production attention kernel over n_sent sentences of
  * exactly len tokens (random q/k/v, CUDA events). */
 BERT_API int32_t bertx_bench_attention(int32_t n_sent, int32_t len, int32_t n_head, int32_t d_head, int32_t reps,

@@ -116,6 +116,31 @@ def test_fused_attention_matches_reference_kernel(pkg, n_sent, L, nh, d, flags):
     assert np.isfinite(err) and err <= 6e-3 * max(ref, 1.0), (err, ref)
 
 
+ATTN_NP_CASES = [([5, 64, 1, 130, 17], 4, 64), ([33] * 20 + [7] * 30, 12, 32), ([512, 3], 2, 64), ([200, 100, 60, 60], 6, 32)]
+
+
+@pytest.mark.parametrize("lens,nh,d", ATTN_NP_CASES, ids=["ragged-d64", "short-d32", "long-d64", "mixed-d32"])
+@pytest.mark.parametrize("flags", [0, 16384], ids=["packed", "unpacked"])
+def test_attention_against_numpy(pkg, lens, nh, d, flags):
+    """The production attention kernels against an independent numpy soft-max attention on the same fp16 inputs (per sentence
+    and head: scores / sqrt(d), soft-max over the sentence's own keys, weighted sum of V; reference bert.cpp:1018-1036) -- not
+    against another CUDA kernel of this repo.  Tolerance: the fp16 rounding of P and of the output, as in the self-test."""
+    qkv, out = pkg.debug_attention(lens, nh, d, seed=11, flags=flags)
+    q, k, v = (qkv[:, i, :].astype(np.float32) for i in range(3))
+    want = np.zeros(out.shape, np.float32)
+    t0 = 0
+    for L in lens:
+        for h in range(nh):
+            sl = slice(h * d, (h + 1) * d)
+            s = q[t0:t0 + L, sl] @ k[t0:t0 + L, sl].T / np.sqrt(np.float32(d))
+            p = np.exp(s - s.max(axis=1, keepdims=True))
+            want[t0:t0 + L, sl] = (p / p.sum(axis=1, keepdims=True)) @ v[t0:t0 + L, sl]
+        t0 += L
+    got = out.astype(np.float32)
+    assert np.isfinite(got).all() and np.abs(want).max() > 0.5
+    assert np.abs(got - want).max() <= 6e-3 * max(float(np.abs(want).max()), 1.0), float(np.abs(got - want).max())
+
+
 # ------------------------------------------------------------------ end-to-end parity
 @pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p)[:-4] for p in GOLDEN])
 def test_encode_matches_reference_golden_embeddings(models, path):
