@@ -125,22 +125,31 @@ int32_t Tokenizer::tokenize(const char * text, int32_t * out, int32_t n_max) con
         for (size_t i = 0; i < len; ++i) { const char c = text[i]; sd[i] = (c >= 'A' && c <= 'Z') ? (char) (c - 'A' + 'a') : c; }
         sn = len;
     } else {
-        // 1. stripAccents (bert.cpp:221-235): walk by utf8_len, fold the 52 mapped letters
+        // 1 + 2 in one walk.  stripAccents (bert.cpp:221-235) copies whole characters by utf8_len and folds the 52 mapped
+        // letters to one ASCII byte; the lower-casing walk (bert.cpp:244-249) then visits exactly the same character starts
+        // (a copied character keeps its lead byte, a folded one is a 1-byte character), so both can be applied per source
+        // character: an upper-case ASCII byte can only be lower-cased where it IS a character (n == 1) or a folded letter.
         for (size_t i = 0; i < len;) {
-            const size_t n = utf8_len(src[i]);
-            if (n == 2 && i + 1 < len) {
-                const char a = accent_fold(src[i], src[i + 1]);
-                if (a) { sd[sn++] = a; i += 2; continue; }
+            const unsigned char c = src[i];
+            if (c < 0x80) {                                           // 1-byte character
+                sd[sn++] = (c >= 'A' && c <= 'Z') ? (char) (c - 'A' + 'a') : (char) c;
+                ++i;
+                continue;
             }
-            const size_t take = i + n <= len ? n : len - i;           // substr clips at the end
-            for (size_t k = 0; k < take; ++k) sd[sn + k] = text[i + k];
-            sn += take;
+            const size_t n = utf8_len(c);
+            if (n == 2 && i + 1 < len) {
+                const char a = accent_fold(c, src[i + 1]);
+                if (a) { sd[sn++] = (a >= 'A' && a <= 'Z') ? (char) (a - 'A' + 'a') : a; i += 2; continue; }
+            }
+            if (i + 4 <= len) {                                       // whole character readable: fixed-size copy
+                memcpy(sd + sn, text + i, 4);                         // (s has 8 spare bytes; only n of the 4 count)
+                sn += n;
+            } else {
+                const size_t take = i + n <= len ? n : len - i;       // substr clips at the end
+                for (size_t k = 0; k < take; ++k) sd[sn + k] = text[i + k];
+                sn += take;
+            }
             i += n;
-        }
-        // 2. ASCII lower-casing at character starts only (bert.cpp:244-249)
-        for (size_t i = 0; i < sn; i += utf8_len((unsigned char) sd[i])) {
-            const char c = sd[i];
-            if (c >= 'A' && c <= 'Z') sd[i] = (char) (c - 'A' + 'a');
         }
     }
     // 3. isolate ASCII punctuation and 3-byte CJK with spaces, byte-wise (bert.cpp:317-339)
