@@ -297,3 +297,32 @@ def test_span_packing_matches_its_definition(pkg):
         for a, b in zip(got[:-1], got[1:]):                             # > 128 tokens only if it is one sentence
             if b - a > 128:
                 assert np.searchsorted(cu, b) - np.searchsorted(cu, a) == 1
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libbert_ref.so")),
+                    reason="oracle/_ref (the compiled reference) is not on this box")
+def test_params_parse_matches_compiled_reference(pkg, tmp_path):
+    """bert_params_parse (bert.cpp:157-193) through both libraries: same fields for every well-formed command line, exit code 0
+    and the 'unknown argument' line for an unknown option, exit 0 for --help.  (A missing or non-numeric value is undefined
+    behaviour in the reference -- std::stoi on argv[argc] -- and is not compared.)"""
+    import subprocess
+    pkg.lib()
+    probe = str(tmp_path / "params_probe")
+    r = subprocess.run(["g++", "-std=c++17", "-O1", "-I", os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "helpers", "params_probe.cpp"),
+                        "-o", probe, "-ldl"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    ours = os.path.join(ROOT, "embeddings.cpp_b200", "lib", "libbert.so")
+    ref = os.path.join(ROOT, "oracle", "_ref", "libbert_ref.so")
+    cases = [[], ["-t", "12"], ["--threads", "3", "--port", "9000"], ["-m", "x/y.bin", "-p", "hello world"],
+             ["--model", "a.bin", "--prompt", "", "-t", "1", "--port", "1"], ["-p", "-t"], ["-t", "7", "-t", "9"]]
+    for args in cases:
+        a = subprocess.run([probe, ours] + args, capture_output=True, text=True)
+        b = subprocess.run([probe, ref] + args, capture_output=True, text=True)
+        assert a.returncode == 0 and b.returncode == 0, (args, a.stderr, b.stderr)
+        assert a.stdout == b.stdout and a.stdout.startswith("ok=1"), (args, a.stdout, b.stdout)
+    for args, needle in ((["--bogus"], "error: unknown argument: --bogus"), (["-h"], "usage:"), (["-t", "2", "--help"], "usage:")):
+        a = subprocess.run([probe, ours] + args, capture_output=True, text=True)
+        b = subprocess.run([probe, ref] + args, capture_output=True, text=True)
+        assert a.returncode == b.returncode == 0, args                       # both exit(0) from inside the parser
+        assert a.stdout == b.stdout == ""                                    # ... before the probe prints anything
+        assert needle in a.stderr and needle in b.stderr, (args, a.stderr)
