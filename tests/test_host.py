@@ -326,3 +326,22 @@ def test_params_parse_matches_compiled_reference(pkg, tmp_path):
         assert a.returncode == b.returncode == 0, args                       # both exit(0) from inside the parser
         assert a.stdout == b.stdout == ""                                    # ... before the probe prints anything
         assert needle in a.stderr and needle in b.stderr, (args, a.stderr)
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libbert_ref.so")),
+                    reason="oracle/_ref (the compiled reference) is not on this box")
+def test_vocab_getters_match_compiled_reference(pkg):
+    """bert_vocab_id_to_token for EVERY id (and a few outside the table), bert_n_embd and bert_n_max_tokens: this library
+    (host-only context) and the compiled reference on the same files (bert.cpp:111-134; duplicates and "##" pieces follow the
+    reference's two-map rules)."""
+    from oracle import reflib
+    for shape, ft in (("tiny-d32", "f16"), ("all-MiniLM-L6-v2", "q4_0"), ("bge-small-zh-v1.5", "q4_1")):
+        model = synth.model_path(shape, ft)
+        ref = reflib.RefBert(model)
+        m = pkg.BertModel(model, host_only=True)
+        assert m.n_embd == ref.n_embd and m.n_max_tokens == ref.n_max_tokens
+        n_vocab = m.hparams()["n_vocab"]
+        for i in list(range(-3, n_vocab + 3)) + [2 ** 31 - 1, -2 ** 31]:
+            assert m.id_to_token(i) == ref.lib.bert_vocab_id_to_token(ref.ctx, i), (shape, i)
+        m.close()
+        ref.close()
