@@ -114,7 +114,7 @@ int32_t Tokenizer::tokenize(const char * text, int32_t * out, int32_t n_max) con
 
     // The two work strings keep their capacity from call to call (no allocation per sentence) and are written through raw
     // pointers into space sized for the worst case (no per-byte capacity checks).
-    static thread_local std::string s, t;
+    static thread_local std::string s;
     bool ascii = true;
     for (size_t i = 0; i < len; ++i) ascii &= src[i] < 0x80;
     s.resize(len + 8);
@@ -152,42 +152,25 @@ int32_t Tokenizer::tokenize(const char * text, int32_t * out, int32_t n_max) con
             i += n;
         }
     }
-    // 3. isolate ASCII punctuation and 3-byte CJK with spaces, byte-wise (bert.cpp:317-339)
-    t.resize(sn * 3 + 8);                                             // a punctuation byte becomes three
-    char * td = &t[0];
-    size_t tn = 0;
-    const unsigned char * p = reinterpret_cast<const unsigned char *>(sd);
-    for (size_t i = 0; i < sn;) {
-        const size_t n = utf8_len(p[i]);
-        if (n == 1 && is_punct(p[i])) {
-            td[tn++] = ' '; td[tn++] = (char) p[i]; td[tn++] = ' ';
-            i += 1;
-        } else if (n == 3 && is_chinese3(p + i, sn - i)) {
-            const size_t take = sn - i < 3 ? sn - i : 3;              // (is_chinese3 implies all three bytes are there)
-            td[tn++] = ' ';
-            for (size_t k = 0; k < take; ++k) td[tn++] = (char) p[i + k];
-            td[tn++] = ' ';
-            i += 3;
-        } else {
-            td[tn++] = (char) p[i];
-            i += 1;
+    // 3 + 4 + 5 in one scan.  The reference first rewrites the string with a space on either side of every ASCII punctuation
+    // byte and every 3-byte CJK character (byte-wise walk, bert.cpp:317-339), then splits on isspace (341-358) and matches
+    // each word greedily (360-416).  The same words come out of one scan that treats a punctuation byte and a qualifying
+    // CJK character as words of their own: the isolation test of the reference looks at one byte position at a time and
+    // keeps no state, so it can be applied where the word scan stands.
+    static const struct ByteClass {
+        uint8_t c[256];
+        ByteClass() {
+            for (int v = 0; v < 256; ++v) {
+                c[v] = is_space((unsigned char) v) ? 1 : is_punct((unsigned char) v) ? 2 : (v & 0xF0) == 0xE0 ? 3 : 0;
+            }
         }
-    }
-    // 4 + 5. split on isspace, greedy longest match per word (bert.cpp:341-416)
+    } cls;
     int32_t nt = 0;
     out[nt++] = kCls;
     if (n_max == 1) return nt;                                        // no room even for [SEP]
-    const char * tb = td;
-    const size_t tl = tn;
-    size_t l = 0;
-    while (l < tl) {
-        while (l < tl && is_space((unsigned char) tb[l])) ++l;
-        size_t r = l;
-        while (r < tl && !is_space((unsigned char) tb[r])) ++r;
-        if (r == l) break;
-        const char * w = tb + l;
-        const size_t n = r - l;
-        l = r;
+    const unsigned char * p = reinterpret_cast<const unsigned char *>(sd);
+    // greedy longest match of one word (bert.cpp:360-416)
+    auto match_word = [&](const char * w, size_t n) {
         const int32_t prev = nt;
         size_t i = 0;
         const VocabTable * map = &token_to_id_;
@@ -210,6 +193,20 @@ int32_t Tokenizer::tokenize(const char * text, int32_t * out, int32_t n_max) con
             maxlen = max_sub_len_;
         }
         if (prev == nt && nt < n_max - 1) out[nt++] = kUnk;           // bounded, unlike bert.cpp:408-412
+    };
+    for (size_t i = 0; i < sn;) {
+        const uint8_t k = cls.c[p[i]];
+        if (k == 1) { ++i; continue; }                                // white space
+        if (k == 2) { match_word(sd + i, 1); ++i; continue; }         // a punctuation byte is a word
+        if (k == 3 && is_chinese3(p + i, sn - i)) { match_word(sd + i, 3); i += 3; continue; }   // so is a CJK character
+        size_t j = i + 1;                                             // an ordinary word: up to the next space / punctuation / CJK
+        for (;;) {
+            while (j < sn && cls.c[p[j]] == 0) ++j;
+            if (j < sn && cls.c[p[j]] == 3 && !is_chinese3(p + j, sn - j)) { ++j; continue; }   // a 0xE? byte that stays in the word
+            break;
+        }
+        match_word(sd + i, j - i);
+        i = j;
     }
     out[nt++] = kSep;
     return nt;

@@ -2,7 +2,8 @@
 // input the reference handles without overrunning its buffer.  Same byte-level algorithm
 // (accent strip -> ASCII lower-case -> isolate ASCII punctuation and 3-byte CJK ->
 // split on isspace -> greedy longest-prefix match with the two vocab maps), implemented
-// over flat hash tables with a bounded match length instead of std::map + O(n^2) substr.
+// as two scans (fold + lower-case; classify + split + match) over flat hash tables with a
+// bounded match length instead of std::map + O(n^2) substr and three rewritten strings.
 #pragma once
 #include <cstdint>
 #include <cstring>
